@@ -1,0 +1,101 @@
+"""ctypes binding of libgsb.so (the C ABI declared in include/gsb.h).
+
+There is NO fallback: if the library is missing or a call fails this module
+raises.  The oracle under oracle/ is never imported from here.
+"""
+from __future__ import annotations
+
+import ctypes as ct
+import os
+import re
+from typing import Optional
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libgsb.so")
+HEADER_PATH = os.path.join(os.path.dirname(_HERE), "include", "gsb.h")
+
+_p = ct.c_void_p
+_i = ct.c_int
+_l = ct.c_int64
+_f = ct.c_float
+_z = ct.c_size_t
+
+# name -> (restype, argtypes); mirrors include/gsb.h one to one
+SIGNATURES = {
+    "gsb_version": (_i, []),
+    "gsb_last_error": (ct.c_char_p, []),
+    "gsb_read_i64_host": (_i, [_p, _p, _p]),
+    "gsb_project_fwd": (_i, [_p] * 8 + [_i, _i, _i, _i, _f, _f, _f, _f, _i, _i] + [_p] * 4 + [_p]),
+    "gsb_project_bwd": (_i, [_p] * 8 + [_i, _i, _i, _i, _f] + [_p, _p, _p, _l, _p, _i] + [_p] * 7 + [_p]),
+    "gsb_pack_visible": (_i, [_p] * 4 + [_i, _i] + [_p] * 5 + [_p]),
+    "gsb_scan_workspace_bytes": (_z, [_l]),
+    "gsb_scan_i32_i64": (_i, [_p, _l, _i, _p, _p, _z, _p]),
+    "gsb_isect_emit": (_i, [_p] * 4 + [_i, _i, _i, _i, _i, _p, _p, _p]),
+    "gsb_sort_workspace_bytes": (_z, [_l]),
+    "gsb_sort_pairs": (_i, [_p] * 4 + [_l, _i, _p, _z, _p]),
+    "gsb_isect_offsets": (_i, [_p, _l, _i, _i, _i, _i, _p, _p]),
+    "gsb_composite_fwd": (_i, [_p] * 4 + [_i] * 6 + [_l, _f] + [_p] * 4 + [_p]),
+    "gsb_composite_bwd": (_i, [_p] * 4 + [_i] * 6 + [_l] + [_p] * 6 + [_p]),
+}
+
+_lib: Optional[ct.CDLL] = None
+
+
+def header_symbols() -> list[str]:
+    """Every function name declared in include/gsb.h."""
+    src = open(HEADER_PATH).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(gsb_[a-z0-9_]+)\s*\(", src)))
+
+
+def lib() -> ct.CDLL:
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(
+                f"{LIB_PATH} is missing: build it with `make` (or __graft_entry__.build()). "
+                "gslam_b200 has no CPU or PyTorch fallback.")
+        L = ct.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(L, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = L
+    return _lib
+
+
+class GsbError(RuntimeError):
+    pass
+
+
+def check(code: int, what: str) -> None:
+    if code != 0:
+        msg = lib().gsb_last_error().decode(errors="replace")
+        raise GsbError(f"{what} failed with code {code}: {msg}")
+
+
+def ptr(t: Optional[torch.Tensor]):
+    """Device pointer of a contiguous CUDA tensor (None -> NULL)."""
+    if t is None:
+        return None
+    assert t.is_cuda, "gslam_b200 kernels need CUDA tensors (there is no CPU path)"
+    return t.data_ptr()
+
+
+def stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+_workspaces: dict = {}
+
+
+def workspace(kind: str, nbytes: int, device) -> torch.Tensor:
+    """A cached scratch buffer per (kind, device, stream), grown geometrically."""
+    key = (kind, str(device), stream())
+    buf = _workspaces.get(key)
+    if buf is None or buf.numel() < nbytes:
+        buf = torch.empty(max(int(nbytes * 1.5), 1 << 16), dtype=torch.uint8, device=device)
+        _workspaces[key] = buf
+    return buf

@@ -1,0 +1,253 @@
+"""Autograd operators over libgsb.so.
+
+Two autograd nodes, as the reference needs (``out.means2d.retain_grad()`` at
+gslam/backend.py:326 makes means2d a real intermediate):
+
+    project   : Gaussian params + cameras -> radii, means2d, rec, tiles_per_gauss
+    composite : rec (+ means2d for gradient routing) -> render, alphas, n_touched
+
+``rec`` is the 12-float splat record documented in include/gsb.h.
+"""
+from __future__ import annotations
+
+import math
+from typing import Optional
+
+import torch
+from torch import Tensor
+
+from . import _lib
+from ._lib import check, lib, ptr, stream
+
+REC = 12
+CH = 5
+TILE = 16
+
+
+def _c(t: Optional[Tensor]) -> Optional[Tensor]:
+    if t is None:
+        return None
+    if t.dtype != torch.float32:
+        raise TypeError(f"gslam_b200 kernels are float32 only, got {t.dtype}")
+    return t.contiguous()
+
+
+def tile_bits(tile_w: int, tile_h: int, n_cameras: int):
+    return (int(math.floor(math.log2(tile_w * tile_h))) + 1,
+            int(math.floor(math.log2(n_cameras))) + 1)
+
+
+class _Project(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, means, quats, log_scales, logit_opacities, logit_colors, log_unc, viewmats, Ks,
+                width, height, eps2d, near_plane, far_plane, radius_clip, tile_w, tile_h):
+        means, quats, log_scales = _c(means), _c(quats), _c(log_scales)
+        logit_opacities, logit_colors, log_unc = _c(logit_opacities), _c(logit_colors), _c(log_unc)
+        viewmats, Ks = _c(viewmats), _c(Ks)
+        N, C = means.shape[0], viewmats.shape[0]
+        dev = means.device
+        radii = torch.empty(C, N, dtype=torch.int32, device=dev)
+        tiles = torch.empty(C, N, dtype=torch.int32, device=dev)
+        means2d = torch.empty(C, N, 2, dtype=torch.float32, device=dev)
+        rec = torch.empty(C, N, REC, dtype=torch.float32, device=dev)
+        check(lib().gsb_project_fwd(
+            ptr(means), ptr(quats), ptr(log_scales), ptr(logit_opacities), ptr(logit_colors),
+            ptr(log_unc), ptr(viewmats), ptr(Ks), C, N, width, height, eps2d, near_plane, far_plane,
+            radius_clip, tile_w, tile_h, ptr(radii), ptr(means2d), ptr(rec), ptr(tiles), stream()),
+            "gsb_project_fwd")
+        ctx.save_for_backward(means, quats, log_scales, logit_opacities, logit_colors, log_unc,
+                              viewmats, Ks, radii, rec)
+        ctx.dims = (C, N, width, height, eps2d)
+        ctx.mark_non_differentiable(radii, tiles)
+        return radii, means2d, rec, tiles
+
+    @staticmethod
+    def backward(ctx, _g_radii, g_means2d, g_rec, _g_tiles):
+        (means, quats, log_scales, logit_opacities, logit_colors, log_unc, viewmats, Ks, radii,
+         rec) = ctx.saved_tensors
+        C, N, width, height, eps2d = ctx.dims
+        dev = means.device
+        if g_rec is None:
+            g_rec = torch.zeros(C, N, REC, dtype=torch.float32, device=dev)
+        g_rec = g_rec.contiguous()
+        if g_means2d is None:
+            g_means2d = torch.zeros(C, N, 2, dtype=torch.float32, device=dev)
+        # a [..., 0:2] view of a record-shaped tensor is read in place (stride 12)
+        if g_means2d.stride() == (N * REC, REC, 1):
+            m2_stride = REC
+        else:
+            g_means2d = g_means2d.contiguous()
+            m2_stride = 2
+        need = ctx.needs_input_grad
+        need_gauss = any(need[:6])
+        need_view = need[6]
+        if need_gauss:
+            # one flat buffer, means|quats|scales|opacities|colors|log_unc, so that a
+            # view-sharded mapping step can all-reduce the six gradients in ONE call
+            flat = torch.empty(N * 15, dtype=torch.float32, device=dev)
+            v_means = flat[0:3 * N].view(N, 3)
+            v_quats = flat[3 * N:7 * N].view(N, 4)
+            v_scales = flat[7 * N:10 * N].view(N, 3)
+            v_opac = flat[10 * N:11 * N]
+            v_colors = flat[11 * N:14 * N].view(N, 3)
+            v_unc = flat[14 * N:15 * N]
+            if log_unc is None:
+                v_unc.zero_()
+        else:
+            v_means = v_quats = v_scales = v_opac = v_colors = v_unc = None
+        v_view = torch.zeros(C, 4, 4, dtype=torch.float32, device=dev) if need_view else None
+        if need_gauss or need_view:
+            check(lib().gsb_project_bwd(
+                ptr(means), ptr(quats), ptr(log_scales), ptr(logit_opacities), ptr(logit_colors),
+                ptr(log_unc), ptr(viewmats), ptr(Ks), C, N, width, height, eps2d, ptr(radii), ptr(rec),
+                ptr(g_means2d), m2_stride, ptr(g_rec), int(need_gauss), ptr(v_means), ptr(v_quats),
+                ptr(v_scales), ptr(v_opac), ptr(v_colors), ptr(v_unc), ptr(v_view), stream()),
+                "gsb_project_bwd")
+        grads = [v_means, v_quats, v_scales, v_opac, v_colors,
+                 v_unc if log_unc is not None else None]
+        grads = [g if n else None for g, n in zip(grads, need[:6])]
+        return (*grads, v_view, None, None, None, None, None, None, None, None, None)
+
+
+class _Composite(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, rec, means2d, flatten_ids, offsets, backgrounds, width, height, tile_w, tile_h,
+                visibility_min_T, count_touched):
+        # means2d is not read (the record carries x,y); it is an input only so that its
+        # gradient is delivered as a separate autograd edge.
+        C, N = rec.shape[0], rec.shape[1]
+        dev = rec.device
+        n_isects = flatten_ids.numel()
+        backgrounds = _c(backgrounds)
+        render = torch.empty(C, height, width, CH, dtype=torch.float32, device=dev)
+        alphas = torch.empty(C, height, width, 1, dtype=torch.float32, device=dev)
+        last_ids = torch.empty(C, height, width, dtype=torch.int32, device=dev)
+        n_touched = torch.zeros(C, N, dtype=torch.int32, device=dev) if count_touched else None
+        check(lib().gsb_composite_fwd(
+            ptr(rec), ptr(flatten_ids), ptr(offsets), ptr(backgrounds), C, N, width, height, tile_w,
+            tile_h, n_isects, visibility_min_T, ptr(render), ptr(alphas), ptr(last_ids),
+            ptr(n_touched), stream()), "gsb_composite_fwd")
+        ctx.save_for_backward(rec, flatten_ids, offsets, backgrounds, alphas, last_ids)
+        ctx.dims = (C, N, width, height, tile_w, tile_h)
+        if n_touched is None:
+            n_touched = torch.zeros(C, N, dtype=torch.int32, device=dev)
+        ctx.mark_non_differentiable(n_touched)
+        return render, alphas, n_touched
+
+    @staticmethod
+    def backward(ctx, v_render, v_alphas, _g_touched):
+        rec, flatten_ids, offsets, backgrounds, alphas, last_ids = ctx.saved_tensors
+        C, N, width, height, tile_w, tile_h = ctx.dims
+        dev = rec.device
+        if v_render is None:
+            v_render = torch.zeros(C, height, width, CH, dtype=torch.float32, device=dev)
+        v_render = v_render.contiguous()
+        v_alphas = v_alphas.contiguous() if v_alphas is not None else None
+        v_rec = torch.zeros(C, N, REC, dtype=torch.float32, device=dev)
+        need_bg = backgrounds is not None and ctx.needs_input_grad[4]
+        v_bg = torch.zeros(C, CH, dtype=torch.float32, device=dev) if need_bg else None
+        check(lib().gsb_composite_bwd(
+            ptr(rec), ptr(flatten_ids), ptr(offsets), ptr(backgrounds), C, N, width, height, tile_w,
+            tile_h, flatten_ids.numel(), ptr(alphas), ptr(last_ids), ptr(v_render), ptr(v_alphas),
+            ptr(v_rec), ptr(v_bg), stream()), "gsb_composite_bwd")
+        # x,y gradients travel on the means2d edge; _Project.backward ignores those two slots of v_rec
+        return v_rec, v_rec[..., 0:2], None, None, v_bg, None, None, None, None, None, None
+
+
+def project(means, quats, log_scales, logit_opacities, logit_colors, log_unc, viewmats, Ks, width,
+            height, eps2d=0.3, near_plane=0.01, far_plane=1e10, radius_clip=0.0):
+    tile_w, tile_h = math.ceil(width / TILE), math.ceil(height / TILE)
+    return _Project.apply(means, quats, log_scales, logit_opacities, logit_colors, log_unc, viewmats,
+                          Ks, int(width), int(height), float(eps2d), float(near_plane),
+                          float(far_plane), float(radius_clip), tile_w, tile_h)
+
+
+@torch.no_grad()
+def inclusive_scan(x_i32: Tensor, flag_positive: bool = False) -> Tensor:
+    n = x_i32.numel()
+    out = torch.empty(n, dtype=torch.int64, device=x_i32.device)
+    if n:
+        nbytes = lib().gsb_scan_workspace_bytes(n)
+        ws = _lib.workspace("scan", nbytes, x_i32.device)
+        check(lib().gsb_scan_i32_i64(ptr(x_i32), n, int(flag_positive), ptr(out), ptr(ws), ws.numel(),
+                                     stream()), "gsb_scan_i32_i64")
+    return out
+
+
+def read_i64(t: Tensor, index: int = -1) -> int:
+    """The one explicit device->host sync of the path."""
+    import ctypes as ct
+    if t.numel() == 0:
+        return 0
+    host = ct.c_int64(0)
+    src = t.data_ptr() + (index % t.numel()) * 8
+    check(lib().gsb_read_i64_host(src, ct.addressof(host), stream()), "gsb_read_i64_host")
+    return int(host.value)
+
+
+@torch.no_grad()
+def sort_pairs(keys: Tensor, vals: Tensor, end_bit: int):
+    """Stable radix sort of (int64 key, int32 value); clobbers the inputs."""
+    n = keys.numel()
+    keys_out, vals_out = torch.empty_like(keys), torch.empty_like(vals)
+    if n:
+        nbytes = lib().gsb_sort_workspace_bytes(n)
+        ws = _lib.workspace("sort", nbytes, keys.device)
+        check(lib().gsb_sort_pairs(ptr(keys), ptr(vals), ptr(keys_out), ptr(vals_out), n, end_bit,
+                                   ptr(ws), ws.numel(), stream()), "gsb_sort_pairs")
+    return keys_out, vals_out
+
+
+@torch.no_grad()
+def isect_tiles(means2d, radii, rec, tiles_per_gauss, tile_w, tile_h, sort=True):
+    """K4 (reference gslam/rasterization.py:261-272): -> isect_ids[I] i64, flatten_ids[I] i32."""
+    C, N = radii.shape
+    dev = radii.device
+    tile_n_bits, cam_n_bits = tile_bits(tile_w, tile_h, C)
+    cum = inclusive_scan(tiles_per_gauss.view(-1))
+    n_isects = read_i64(cum)
+    isect_ids = torch.empty(n_isects, dtype=torch.int64, device=dev)
+    flatten_ids = torch.empty(n_isects, dtype=torch.int32, device=dev)
+    if n_isects:
+        check(lib().gsb_isect_emit(ptr(means2d), ptr(radii), ptr(rec), ptr(cum), C, N, tile_w, tile_h,
+                                   tile_n_bits, ptr(isect_ids), ptr(flatten_ids), stream()),
+              "gsb_isect_emit")
+        if sort:
+            isect_ids, flatten_ids = sort_pairs(isect_ids, flatten_ids, 32 + tile_n_bits + cam_n_bits)
+    return isect_ids, flatten_ids
+
+
+@torch.no_grad()
+def isect_offset_encode(isect_ids, n_cameras, tile_w, tile_h):
+    """K5 (reference gslam/rasterization.py:274)."""
+    tile_n_bits, _ = tile_bits(tile_w, tile_h, n_cameras)
+    offsets = torch.empty(n_cameras, tile_h, tile_w, dtype=torch.int32, device=isect_ids.device)
+    check(lib().gsb_isect_offsets(ptr(isect_ids), isect_ids.numel(), n_cameras, tile_w, tile_h,
+                                  tile_n_bits, ptr(offsets), stream()), "gsb_isect_offsets")
+    return offsets
+
+
+def composite(rec, means2d, flatten_ids, offsets, backgrounds, width, height, visibility_min_T=0.5,
+              count_touched=True):
+    tile_w, tile_h = math.ceil(width / TILE), math.ceil(height / TILE)
+    return _Composite.apply(rec, means2d, flatten_ids, offsets, backgrounds, int(width), int(height),
+                            tile_w, tile_h, float(visibility_min_T), bool(count_touched))
+
+
+@torch.no_grad()
+def pack_visible(radii, means2d, rec):
+    """K3 compaction (reference gslam/rasterization.py:409-419)."""
+    C, N = radii.shape
+    dev = radii.device
+    cum = inclusive_scan(radii.view(-1), flag_positive=True)
+    nnz = read_i64(cum)
+    camera_ids = torch.empty(nnz, dtype=torch.int64, device=dev)
+    gaussian_ids = torch.empty(nnz, dtype=torch.int64, device=dev)
+    radii_out = torch.empty(nnz, dtype=torch.int32, device=dev)
+    means2d_out = torch.empty(nnz, 2, dtype=torch.float32, device=dev)
+    depths_out = torch.empty(nnz, dtype=torch.float32, device=dev)
+    if nnz:
+        check(lib().gsb_pack_visible(ptr(radii), ptr(means2d), ptr(rec), ptr(cum), C, N,
+                                     ptr(camera_ids), ptr(gaussian_ids), ptr(radii_out),
+                                     ptr(means2d_out), ptr(depths_out), stream()), "gsb_pack_visible")
+    return camera_ids, gaussian_ids, radii_out, means2d_out, depths_out

@@ -1,0 +1,195 @@
+"""Drop-in for reference ``gslam/rasterization.py`` backed by libgsb.so.
+
+Same call surface (``rasterization(...) -> RasterizationOutput``,
+``get_new_splat_depth``; reference gslam/rasterization.py:17-71, :363-383) for
+the argument subset its callers use (gslam/map.py:59-74, :88-103,
+gslam/insertion.py:252); anything else raises NotImplementedError.  There is
+no CPU path and no fallback.
+"""
+from __future__ import annotations
+
+import math
+from dataclasses import dataclass
+from typing import ClassVar, Optional
+
+import torch
+from torch import Tensor
+from typing_extensions import Literal
+
+from . import ops
+
+
+@dataclass
+class RasterizationOutput:
+    """Field order matters: gslam/backend.py:619 builds it positionally."""
+    per_gaussian_params: ClassVar[tuple[str]] = ('radii', 'means2d')
+    rgbs: torch.Tensor = None
+    alphas: torch.Tensor = None
+    depthmaps: torch.Tensor = None
+    betas: torch.Tensor = None
+    tile_width: int = None
+    tile_height: int = None
+    tiles_per_gauss: torch.Tensor = None
+    isect_ids: torch.Tensor = None
+    flatten_ids: torch.Tensor = None
+    isect_offsets: torch.Tensor = None
+    width: int = None
+    height: int = None
+    tile_size: int = None
+    n_cameras: int = None
+    camera_ids: torch.Tensor = None
+    gaussian_ids: torch.Tensor = None
+    radii: torch.Tensor = None
+    means2d: torch.Tensor = None
+    depths: torch.Tensor = None
+    conics: torch.Tensor = None
+    opacities: torch.Tensor = None
+    n_touched: torch.Tensor = None
+
+
+def _unsupported(what: str):
+    raise NotImplementedError(
+        f"gslam_b200.rasterization: {what} is outside the subset gslam uses "
+        "(SURVEY.md 8b); there is no fallback path")
+
+
+def rasterization(
+    means: Tensor,  # [N, 3]
+    quats: Tensor,  # [N, 4]
+    log_scales: Tensor,  # [N, 3]
+    logit_opacities: Tensor,  # [N]
+    logit_colors: Tensor,  # [N, 3]
+    viewmats: Tensor,  # [C, 4, 4]
+    Ks: Tensor,  # [C, 3, 3]
+    width: int,
+    height: int,
+    near_plane: float = 0.01,
+    far_plane: float = 1e10,
+    radius_clip: float = 0.0,
+    eps2d: float = 0.3,
+    packed: bool = True,
+    tile_size: int = 16,
+    backgrounds: Optional[Tensor] = None,
+    render_mode: Literal["RGB", "D", "ED", "RGB+D", "RGB+ED"] = "RGB",
+    sparse_grad: bool = False,
+    absgrad: bool = False,
+    rasterize_mode: Literal["classic", "antialiased"] = "classic",
+    channel_chunk: int = 32,
+    camera_model: Literal["pinhole", "ortho", "fisheye"] = "pinhole",
+    covars: Optional[Tensor] = None,
+    log_uncertainties: Optional[Tensor] = None,
+    visibility_min_T: float = 0.5,
+    mask: Optional[Tensor] = None,
+) -> RasterizationOutput:
+    """Rasterize N Gaussians to C image planes; see the reference docstring
+    (gslam/rasterization.py:72-119) for the argument meanings."""
+    N = means.shape[0]
+    C = viewmats.shape[0]
+    assert means.shape == (N, 3), means.shape
+    assert quats.shape == (N, 4), quats.shape
+    assert log_scales.shape == (N, 3), log_scales.shape
+    assert logit_opacities.shape == (N,), logit_opacities.shape
+    assert viewmats.shape == (C, 4, 4), viewmats.shape
+    assert Ks.shape == (C, 3, 3), Ks.shape
+    assert render_mode in ["RGB", "D", "ED", "RGB+D", "RGB+ED"], render_mode
+    if packed:
+        _unsupported("packed=True (use get_new_splat_depth for the packed projection)")
+    if covars is not None:
+        _unsupported("covars")
+    if tile_size != ops.TILE:
+        _unsupported(f"tile_size={tile_size}")
+    if render_mode in ("ED", "RGB+ED"):
+        _unsupported(f"render_mode={render_mode!r} (raises KeyError in the reference too, :344)")
+    if sparse_grad or absgrad:
+        _unsupported("sparse_grad / absgrad")
+    if rasterize_mode != "classic" or camera_model != "pinhole":
+        _unsupported("rasterize_mode / camera_model other than classic / pinhole")
+    if logit_colors.dim() != 2 or logit_colors.shape != (N, 3):
+        _unsupported(f"logit_colors of shape {tuple(logit_colors.shape)} (only [N,3])")
+    if not means.is_cuda:
+        raise RuntimeError("gslam_b200.rasterization needs CUDA tensors; there is no CPU path")
+
+    tile_width = math.ceil(width / float(tile_size))
+    tile_height = math.ceil(height / float(tile_size))
+
+    # K8+K1 (+ tile counting): activations, projection and record packing in one kernel
+    radii, means2d, rec, tiles_per_gauss = ops.project(
+        means, quats, log_scales, logit_opacities, logit_colors, log_uncertainties, viewmats, Ks,
+        width, height, eps2d, near_plane, far_plane, radius_clip)
+
+    # K4+K5
+    isect_ids, flatten_ids = ops.isect_tiles(means2d, radii, rec, tiles_per_gauss, tile_width,
+                                             tile_height)
+    isect_offsets = ops.isect_offset_encode(isect_ids, C, tile_width, tile_height)
+
+    # backgrounds [C,3] -> [C,5] = (r, g, b, 0, e)   (reference :236-255)
+    bg5 = None
+    if backgrounds is not None:
+        bg5 = torch.zeros(C, ops.CH, dtype=torch.float32, device=means.device)
+        if render_mode != "D":
+            bg5[:, :3] = backgrounds
+        if log_uncertainties is not None:
+            bg5[:, 4] = math.e
+
+    # K6
+    render, alphas, n_touched = ops.composite(rec, means2d, flatten_ids, isect_offsets, bg5, width,
+                                              height, visibility_min_T)
+
+    out = RasterizationOutput(
+        rgbs=render[..., :3] if render_mode not in ("D",) else None,
+        alphas=alphas,
+        depthmaps=render[..., 3] if render_mode in ("D", "RGB+D") else None,
+        betas=render[..., 4] if log_uncertainties is not None else None,
+        tile_width=tile_width,
+        tile_height=tile_height,
+        tiles_per_gauss=tiles_per_gauss,
+        isect_ids=isect_ids,
+        flatten_ids=flatten_ids,
+        isect_offsets=isect_offsets,
+        width=width,
+        height=height,
+        tile_size=tile_size,
+        n_cameras=C,
+        camera_ids=None,
+        gaussian_ids=None,
+        radii=radii,
+        means2d=means2d,
+        depths=rec[..., 9],
+        conics=rec[..., 3:6],
+        opacities=rec[..., 2],
+        n_touched=n_touched.long(),
+    )
+    return out
+
+
+def get_new_splat_depth(
+    new_params: dict[str, torch.Tensor],
+    viewmats: Tensor,  # [C, 4, 4]
+    Ks: Tensor,  # [C, 3, 3]
+    width: int,
+    height: int,
+    near_plane: float = 0.01,
+    far_plane: float = 1e10,
+    radius_clip: float = 0.0,
+    eps2d: float = 0.3,
+    packed: bool = True,
+    sparse_grad: bool = False,
+    rasterize_mode: Literal["classic", "antialiased"] = "classic",
+    camera_model: Literal["pinhole", "ortho", "fisheye"] = "pinhole",
+    covars: Optional[Tensor] = None,
+):
+    """Projection only (reference gslam/rasterization.py:363-448); 'scales' are log-scales (:386-387)."""
+    if covars is not None or rasterize_mode != "classic" or camera_model != "pinhole" or sparse_grad:
+        _unsupported("covars / antialiased / non-pinhole / sparse_grad")
+    means = new_params['means']
+    quats = new_params['quats']
+    log_scales = new_params['scales']
+    N = means.shape[0]
+    zeros = torch.zeros(N, dtype=torch.float32, device=means.device)
+    with torch.no_grad():
+        radii, means2d, rec, _ = ops.project(
+            means, quats, log_scales, zeros, zeros[:, None].expand(N, 3), None, viewmats, Ks,
+            width, height, eps2d, near_plane, far_plane, radius_clip)
+        if packed:
+            return ops.pack_visible(radii, means2d, rec)
+        return radii, means2d, rec[..., 9]

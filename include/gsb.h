@@ -1,0 +1,126 @@
+/* gsb.h -- C ABI of libgsb.so, the sm_100a kernels behind gslam's rasterization
+ * hot path (reference: /root/reference/gslam/rasterization.py).
+ *
+ * Conventions:
+ *  - every pointer is a DEVICE pointer unless its name ends in _host;
+ *  - the caller owns all memory; the library never allocates device memory and
+ *    keeps no global mutable state except a per-thread last-error string;
+ *  - all work is enqueued on `stream` (a cudaStream_t passed as void*); no
+ *    call synchronises the device except gsb_read_i64_host;
+ *  - every entry point returns 0 on success, a positive cudaError_t or a
+ *    negative GSB_E* code on failure; nothing throws or exits.
+ *
+ * Splat record ("rec"), one per (camera, Gaussian), 12 floats = 48 bytes:
+ *    [0] x  [1] y  [2] opacity  [3] conic a  [4] conic b  [5] conic c
+ *    [6] r  [7] g  [8] b        [9] depth   [10] beta    [11] unused (0)
+ * It replaces the separate means2d / conics / opacities / colors tensors that
+ * the reference builds at gslam/rasterization.py:153-256; the gradient record
+ * v_rec has the same layout.
+ */
+#ifndef GSB_H
+#define GSB_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GSB_REC 12            /* floats per splat record              */
+#define GSB_CH 5              /* composited channels: r g b depth beta */
+#define GSB_TILE 16           /* tile edge in pixels (reference tile_size=16) */
+
+#define GSB_EINVAL (-1)       /* bad argument                         */
+#define GSB_EWORKSPACE (-2)   /* workspace too small                  */
+
+int gsb_version(void);
+const char* gsb_last_error(void);
+
+/* Blocking 8-byte device->host read (the one explicit sync of the path: the
+ * intersection count that sizes the key buffers; upstream hides the same sync
+ * inside isect_tiles, reference gslam/rasterization.py:261). */
+int gsb_read_i64_host(const int64_t* src, int64_t* dst_host, void* stream);
+
+/* K1+K8: activations + EWA projection + tile counting, unpacked.
+ * Replaces gslam/rasterization.py:145-170, :187, :225-256 and the counting
+ * half of isect_tiles (:261).  log_unc may be NULL (beta record slot = 0).
+ * Outputs: radii[C,N] i32, means2d[C,N,2], rec[C,N,12], tiles_per_gauss[C,N] i32. */
+int gsb_project_fwd(const float* means, const float* quats, const float* log_scales,
+                    const float* logit_opacities, const float* logit_colors,
+                    const float* log_unc, const float* viewmats, const float* Ks,
+                    int C, int N, int width, int height, float eps2d, float near_plane,
+                    float far_plane, float radius_clip, int tile_w, int tile_h,
+                    int32_t* radii, float* means2d, float* rec, int32_t* tiles_per_gauss,
+                    void* stream);
+
+/* K2+K8 backward.  v_rec[C,N,12] carries the gradients of every record slot
+ * except x,y, which come from v_means2d (element stride `v_means2d_stride`
+ * floats between consecutive (c,n) rows, so a [.., 0:2] view of v_rec works).
+ * Outputs (overwritten, summed over cameras): v_means[N,3] v_quats[N,4]
+ * v_log_scales[N,3] v_logit_opacities[N] v_logit_colors[N,3] v_log_unc[N]
+ * (any may be NULL when need_gauss_grads == 0) and v_viewmats[C,4,4] (must be
+ * zeroed by the caller; accumulated atomically; may be NULL). */
+int gsb_project_bwd(const float* means, const float* quats, const float* log_scales,
+                    const float* logit_opacities, const float* logit_colors,
+                    const float* log_unc, const float* viewmats, const float* Ks,
+                    int C, int N, int width, int height, float eps2d,
+                    const int32_t* radii, const float* rec,
+                    const float* v_means2d, int64_t v_means2d_stride, const float* v_rec,
+                    int need_gauss_grads,
+                    float* v_means, float* v_quats, float* v_log_scales,
+                    float* v_logit_opacities, float* v_logit_colors, float* v_log_unc,
+                    float* v_viewmats, void* stream);
+
+/* K3: packed projection (reference gslam/rasterization.py:390-419).  Two calls:
+ * gsb_project_fwd (unpacked) then gsb_pack_visible compacts the rows with
+ * radii > 0 in (c, n) order.  `cum` is the inclusive scan of (radii > 0). */
+int gsb_pack_visible(const int32_t* radii, const float* means2d, const float* rec,
+                     const int64_t* cum, int C, int N, int64_t* camera_ids,
+                     int64_t* gaussian_ids, int32_t* radii_out, float* means2d_out,
+                     float* depths_out, void* stream);
+
+/* Inclusive int32 -> int64 scan (cumsum of tiles_per_gauss; the last element is
+ * the intersection count I).  flag_positive != 0 scans (x > 0) instead of x. */
+size_t gsb_scan_workspace_bytes(int64_t n);
+int gsb_scan_i32_i64(const int32_t* in, int64_t n, int flag_positive, int64_t* out,
+                     void* workspace, size_t workspace_bytes, void* stream);
+
+/* K4: emit one (key, value) per (Gaussian, tile).  key = cam << (32+tile_n_bits)
+ * | tile << 32 | bits(depth); value = c*N + n. */
+int gsb_isect_emit(const float* means2d, const int32_t* radii, const float* rec,
+                   const int64_t* cum, int C, int N, int tile_w, int tile_h,
+                   int tile_n_bits, int64_t* isect_ids, int32_t* flatten_ids, void* stream);
+
+/* K4: stable LSD radix sort of (u64 key, i32 value) pairs over bits [0,end_bit).
+ * Sorted data ends in keys_out/vals_out; keys_in/vals_in are clobbered. */
+size_t gsb_sort_workspace_bytes(int64_t n);
+int gsb_sort_pairs(int64_t* keys_in, int32_t* vals_in, int64_t* keys_out, int32_t* vals_out,
+                   int64_t n, int end_bit, void* workspace, size_t workspace_bytes,
+                   void* stream);
+
+/* K5: isect_offset_encode (reference gslam/rasterization.py:274). */
+int gsb_isect_offsets(const int64_t* isect_ids, int64_t n_isects, int C, int tile_w,
+                      int tile_h, int tile_n_bits, int32_t* offsets, void* stream);
+
+/* K6: per-tile front-to-back compositing (reference gslam/rasterization.py:325-339).
+ * backgrounds[C,5] may be NULL.  n_touched[C,N] i32 must be zeroed by the caller
+ * (NULL skips the count).  Outputs render[C,H,W,5], alphas[C,H,W], last_ids[C,H,W]. */
+int gsb_composite_fwd(const float* rec, const int32_t* flatten_ids, const int32_t* offsets,
+                      const float* backgrounds, int C, int N, int width, int height,
+                      int tile_w, int tile_h, int64_t n_isects, float visibility_min_T,
+                      float* render, float* alphas, int32_t* last_ids, int32_t* n_touched,
+                      void* stream);
+
+/* K7: compositing backward.  v_rec[C,N,12] must be zeroed by the caller and is
+ * accumulated atomically (x,y slots hold v_means2d).  v_backgrounds[C,5] may be NULL. */
+int gsb_composite_bwd(const float* rec, const int32_t* flatten_ids, const int32_t* offsets,
+                      const float* backgrounds, int C, int N, int width, int height,
+                      int tile_w, int tile_h, int64_t n_isects, const float* render_alphas,
+                      const int32_t* last_ids, const float* v_render, const float* v_alphas,
+                      float* v_rec, float* v_backgrounds, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GSB_H */
