@@ -1,0 +1,364 @@
+#!/usr/bin/env python
+"""bench.py -- fwd+bwd rasterization throughput of the gslam hot path on B200.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+Workload (BASELINE.json configs[1] shape): 200k Gaussians, 640x480 TUM-fr1
+intrinsics, RGB + depth + beta channels, ONE view per GPU per step.  A step is
+rasterization() forward, the active-NeRF photometric loss, and the backward
+pass to every Gaussian parameter and to the camera viewmat.  With N > 1 the
+views of a mapping window are sharded one per rank (weak scaling) and the six
+Gaussian-parameter gradients are all-reduced over NCCL in one flat buffer.
+
+Prints ONE JSON line (rank 0).  `--impl reference` times the CPU oracle
+(oracle/torch_ref.py, the restatement of the reference's math: the reference's
+own kernels live in un-vendored CUDA extensions and cannot run on a CPU) on the
+box's host cores on a bounded sample of the same workload.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import tempfile
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+N_GAUSS = 200_000
+METRIC = "fwd+bwd rasterize it/s (640x480, 200k Gaussians)"
+UNIT = "it/s"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--n-gauss", type=int, default=N_GAUSS)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return float(d["hbm_gbs"]), "measured", float(d.get("sm_max_mhz", 1965.0))
+    return 6650.0, "fallback", 1965.0
+
+
+# ----------------------------------------------------------------------------------------------
+# CPU arm: the oracle on a bounded sample (a band of tile rows of the same 640x480 view)
+# ----------------------------------------------------------------------------------------------
+def cpu_oracle_rate(n_gauss: int, band_rows: int, reps: int = 1, warm: int = 0):
+    """it/s of the CPU oracle, scaled from a band of `band_rows` tile rows (of 30) to the full view."""
+    import torch
+    from gslam_b200.synthetic import make_scene, target_images
+    from oracle import torch_ref as R
+
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    sc = make_scene(n_gauss, 1, "tum", 1.0)
+    total_rows = (sc.height + 15) // 16
+    band_rows = max(1, min(band_rows, total_rows))
+    h = min(band_rows * 16, sc.height)
+    gt = target_images(1, sc.height, sc.width)[:, :h]
+    times = []
+    for it in range(warm + reps):
+        ps = [p.clone().requires_grad_(True) for p in sc.params()]
+        vm = sc.viewmats.clone().requires_grad_(True)
+        t0 = time.perf_counter()
+        out = R.rasterization(ps[0], ps[1], ps[2], ps[3], ps[4], vm, sc.Ks, sc.width, h,
+                              backgrounds=torch.zeros(1, 3), render_mode="RGB+D", log_uncertainties=ps[5])
+        loss = R.tracking_loss(gt, out.rgbs, out.betas)
+        loss.backward()
+        dt = time.perf_counter() - t0
+        if it >= warm:
+            times.append(dt)
+    frac = h / sc.height
+    t = statistics.median(times)
+    sample = (f"oracle/torch_ref.py fwd+loss+bwd on {n_gauss} Gaussians, rows 0..{h} of the 640x480 view "
+              f"({band_rows}/{total_rows} tile rows), time scaled by {1 / frac:.2f} to a full view")
+    return frac / t, t, cores, sample
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    k = args.steps + args.warmup
+    # ~23 s per full view on 8 cores; keep the whole run near 2-3 minutes
+    band = max(1, min(30, int(30 * 150.0 / (23.0 * max(k, 1)))))
+    value, t, cores, sample = cpu_oracle_rate(args.n_gauss, band, reps=args.steps, warm=args.warmup)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 / value,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic",
+        "config": {"workload": f"cfg2-shape: 1 view, N={args.n_gauss}, 640x480, RGB+D+beta, fwd+bwd",
+                   "note": "CPU oracle (port of the reference math); reference kernels are un-vendored CUDA"},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ----------------------------------------------------------------------------------------------
+# GPU arm
+# ----------------------------------------------------------------------------------------------
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        self.idx = gpu_index
+        self.p = None
+
+    def start(self):
+        try:
+            self.p = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200",
+                 "-i", str(self.idx)], stdout=self.f, stderr=subprocess.DEVNULL)
+        except OSError:
+            self.p = None
+
+    def stop(self):
+        if self.p is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.p.terminate()
+        self.p.wait()
+        self.f.flush()
+        self.f.seek(0)
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.f.read().splitlines():
+            c = [x.strip() for x in ln.split(",")]
+            if len(c) < 9:
+                continue
+            try:
+                sm.append(float(c[1])); mx.append(float(c[2]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, c[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        os.unlink(self.f.name)
+        return {"sm_mhz": statistics.median(sm) if sm else None,
+                "sm_max_mhz": max(mx) if mx else None, "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from gslam_b200 import _lib, ops
+    from gslam_b200.rasterization import rasterization
+    from gslam_b200.synthetic import make_scene, target_images
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU fallback in the product path)"
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    n = args.n_gauss
+    sc = make_scene(n, world, "tum", 1.0)       # one view of the mapping window per rank
+    H, W = sc.height, sc.width
+    host = [p.clone().pin_memory() for p in sc.params()]
+    host_vm = sc.viewmats[rank:rank + 1].clone().pin_memory()
+    host_K = sc.Ks[rank:rank + 1].clone().pin_memory()
+    host_gt = target_images(world, H, W)[rank:rank + 1].clone().pin_memory()
+    params = [h.to(dev).requires_grad_(True) for h in host]
+    vm = host_vm.to(dev).requires_grad_(True)
+    K = host_K.to(dev)
+    gt = host_gt.to(dev)
+    bg = torch.zeros(1, 3, device=dev)
+    flush_buf = torch.empty(256 << 20, dtype=torch.uint8, device=dev)   # 2x the 126 MB L2
+
+    def loss_fn(out, gt_):
+        # active-NeRF photometric term of the tracking / mapping steps
+        # (gslam/frontend.py:113-129, gslam/backend.py:277-283)
+        err = out.rgbs - gt_
+        return (err.square().sum(dim=-1) * out.betas.pow(-2.0)).mean()
+
+    def step(ps, vm_, K_, gt_):
+        for p in ps:
+            p.grad = None
+        vm_.grad = None
+        out = rasterization(ps[0], ps[1], ps[2], ps[3], ps[4], vm_, K_, W, H, packed=False,
+                            render_mode="RGB+D", log_uncertainties=ps[5], backgrounds=bg)
+        loss = loss_fn(out, gt_)
+        loss.backward()
+        if world > 1:
+            # the six gradients are views of one flat [15N] buffer written by project_bwd
+            flat = ps[0].grad._base if ps[0].grad._base is not None else None
+            if flat is not None and flat.numel() == 15 * n:
+                dist.all_reduce(flat)
+            else:
+                for p in ps:
+                    dist.all_reduce(p.grad)
+        return loss, out
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        step(params, vm, K, gt)
+    barrier()
+
+    # ---- timed region: K steps, one CUDA-event pair per step, L2 flushed between steps ----------
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+          for _ in range(args.steps)]
+    launches0 = _lib.launch_count
+    barrier()
+    wall0 = time.perf_counter()
+    for e0, e1 in ev:
+        flush_buf.zero_()
+        e0.record()
+        step(params, vm, K, gt)
+        e1.record()
+    barrier()
+    wall = time.perf_counter() - wall0
+    launches = _lib.launch_count - launches0
+    clocks = sampler.stop() if rank == 0 else None
+    ms = sum(a.elapsed_time(b) for a, b in ev) / args.steps
+    t = torch.tensor([ms], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    value = world * 1e3 / ms
+
+    # ---- per-kernel durations (CUDA events around each C-ABI call, same steps, live) -------------
+    ops.pair_counter = torch.zeros(1, dtype=torch.int64, device=dev)
+    _, out = step(params, vm, K, gt)
+    torch.cuda.synchronize()
+    P = int(ops.pair_counter.item())
+    I = int(out.isect_ids.numel())
+    ops.pair_counter = None
+    del out
+    _lib.start_timing()
+    for _ in range(min(args.steps, 20)):
+        flush_buf.zero_()
+        step(params, vm, K, gt)
+    kt = _lib.stop_timing()
+
+    # ---- e2e: host buffers in, loss + pose gradient out, copies inside the timed region ----------
+    h2d = sum(h.numel() * 4 for h in host) + (host_vm.numel() + host_K.numel() + host_gt.numel()) * 4
+    res_host = torch.empty(17, dtype=torch.float32).pin_memory()
+    d2h = res_host.numel() * 4
+
+    def e2e_step():
+        ps = [h.to(dev, non_blocking=True).requires_grad_(True) for h in host]
+        vm_ = host_vm.to(dev, non_blocking=True).requires_grad_(True)
+        K_ = host_K.to(dev, non_blocking=True)
+        gt_ = host_gt.to(dev, non_blocking=True)
+        loss, _ = step(ps, vm_, K_, gt_)
+        res = torch.cat([loss.detach().view(1), vm_.grad.view(-1)])
+        res_host.copy_(res, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+
+    for _ in range(3):
+        e2e_step()
+    barrier()
+    ev2 = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+           for _ in range(args.steps)]
+    for e0, e1 in ev2:
+        flush_buf.zero_()
+        e0.record()
+        e2e_step()
+        e1.record()
+    barrier()
+    ms2 = sum(a.elapsed_time(b) for a, b in ev2) / args.steps
+    t = torch.tensor([ms2], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_value = world * 1e3 / float(t.item())
+
+    if rank == 0:
+        hbm, which, sm_max = peaks()
+        CN, px = n, H * W
+        # algorithmic bytes per launch, C = 1 view per rank
+        alg = {
+            "gsb_project_fwd": 60 * n + 64 * CN,
+            "gsb_project_bwd": 60 * n + (48 + 8 + 4 + 48) * CN + 60 * n,
+            "gsb_scan_i32_i64": 12 * CN,
+            "gsb_isect_emit": 16 * CN + 12 * I,
+            "gsb_sort_pairs": (24 * 6 + 0) * I,
+            "gsb_isect_offsets": 8 * I + 4 * 1200,
+            "gsb_composite_fwd": 52 * I + (4 * 5 + 8) * px,
+            "gsb_composite_bwd": 52 * I + (8 * 5 + 12) * px + 48 * I,
+        }
+        stages = []
+        for name, (calls, msk) in sorted(kt.items(), key=lambda kv: -kv[1][1]):
+            if name not in alg:
+                continue
+            ach = alg[name] / (msk * 1e-3) / 1e9
+            stages.append({"kernel": name, "ms": round(msk, 5), "bound": "hbm", "achieved": round(ach, 2),
+                           "peak": hbm, "unit": "GB/s", "frac": round(ach / hbm, 5),
+                           "algorithmic_bytes": alg[name]})
+        # FP32 view of the compositing kernels: pairs evaluated x FMA-class instructions per pair
+        fp32_peak = 148 * 128 * sm_max * 1e6          # FMA lanes/s
+        for st in stages:
+            if st["kernel"] == "gsb_composite_fwd":
+                st["fp32"] = {"pairs": P, "flop_per_pair": 2 * (9 + 5) + 1,
+                              "achieved_gpairs_s": round(P / (st["ms"] * 1e-3) / 1e9, 3),
+                              "fma_frac": round(P * (9 + 5) / (st["ms"] * 1e-3) / fp32_peak, 5)}
+            if st["kernel"] == "gsb_composite_bwd":
+                st["fp32"] = {"pairs": P, "flop_per_pair": 45 + 3 * 5 + 1,
+                              "achieved_gpairs_s": round(P / (st["ms"] * 1e-3) / 1e9, 3),
+                              "fma_frac": round(P * 30 / (st["ms"] * 1e-3) / fp32_peak, 5)}
+        dom = stages[0] if stages else None
+        roofline = None
+        if dom:
+            roofline = {"kernel": dom["kernel"], "bound": "hbm", "achieved": dom["achieved"], "peak": hbm,
+                        "unit": "GB/s", "frac": dom["frac"], "traffic": None, "peak_source": which,
+                        "ms_per_launch": dom["ms"]}
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"cfg2-shape: 1 view per GPU, N={n}, 640x480 TUM-fr1, RGB+D+beta, "
+                                   "fwd + active-NeRF loss + bwd (all Gaussian grads + viewmat grad)"
+                                   + (", flat-gradient NCCL all-reduce" if world > 1 else ""),
+                       "l2": "256 MiB memset between timed steps, outside each step's event pair",
+                       "n_isects": I, "pairs": P},
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+            "gpu_launches": launches,
+            "launch_calls_per_step": launches / args.steps,
+            "wall_s_timed_region": wall,
+            "clocks": clocks,
+            "roofline": roofline,
+            "roofline_stages": stages,
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            v, tsec, cores, sample = cpu_oracle_rate(n, band_rows=30, reps=1)
+            line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
+                                    "sample": sample, "seconds": tsec}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    a = parse()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_ours(a)

@@ -36,7 +36,7 @@ SIGNATURES = {
     "gsb_sort_workspace_bytes": (_z, [_l]),
     "gsb_sort_pairs": (_i, [_p] * 4 + [_l, _i, _p, _z, _p]),
     "gsb_isect_offsets": (_i, [_p, _l, _i, _i, _i, _i, _p, _p]),
-    "gsb_composite_fwd": (_i, [_p] * 4 + [_i] * 6 + [_l, _f] + [_p] * 4 + [_p]),
+    "gsb_composite_fwd": (_i, [_p] * 4 + [_i] * 6 + [_l, _f] + [_p] * 5 + [_p]),
     "gsb_composite_bwd": (_i, [_p] * 4 + [_i] * 6 + [_l] + [_p] * 6 + [_p]),
 }
 
@@ -74,6 +74,42 @@ def check(code: int, what: str) -> None:
     if code != 0:
         msg = lib().gsb_last_error().decode(errors="replace")
         raise GsbError(f"{what} failed with code {code}: {msg}")
+
+
+# ---- launch accounting / per-call device timing (used by bench.py) -----------------------
+launch_count = 0          # number of kernel-launching C-ABI calls made so far
+_timing: Optional[dict] = None   # name -> list[(start_event, end_event)] while profiling
+
+# device kernels each entry point enqueues (cub scan: 2, cub radix sort: see sort.cu)
+KERNELS_PER_CALL = {"gsb_read_i64_host": 0}
+
+
+def call(name: str, *args) -> None:
+    """Invoke a kernel-launching entry point, count it, optionally time it with CUDA events."""
+    global launch_count
+    fn = getattr(lib(), name)
+    launch_count += 1
+    if _timing is None:
+        check(fn(*args), name)
+        return
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    check(fn(*args), name)
+    e1.record()
+    _timing.setdefault(name, []).append((e0, e1))
+
+
+def start_timing() -> None:
+    global _timing
+    _timing = {}
+
+
+def stop_timing() -> dict:
+    """-> {entry point: (calls, mean milliseconds per call)}; synchronises."""
+    global _timing
+    t, _timing = _timing or {}, None
+    torch.cuda.synchronize()
+    return {k: (len(v), sum(a.elapsed_time(b) for a, b in v) / len(v)) for k, v in t.items()}
 
 
 def ptr(t: Optional[torch.Tensor]):

@@ -28,13 +28,14 @@ __device__ __forceinline__ TileRange tile_range(const int32_t* offsets, int cam,
     return r;
 }
 
-template <bool COUNT>
+template <bool COUNT, bool STATS>
 __global__ void __launch_bounds__(256)
 composite_fwd_kernel(const float4* __restrict__ rec, const int32_t* __restrict__ flatten_ids,
                      const int32_t* __restrict__ offsets, const float* __restrict__ backgrounds, int C,
                      int width, int height, int tile_w, int tile_h, int64_t n_isects, float min_T,
                      float* __restrict__ render, float* __restrict__ alphas,
-                     int32_t* __restrict__ last_ids, int32_t* __restrict__ n_touched) {
+                     int32_t* __restrict__ last_ids, int32_t* __restrict__ n_touched,
+                     unsigned long long* __restrict__ pair_count) {
     __shared__ float4 s0[BATCH];   // x, y, opacity, a'
     __shared__ float4 s1[BATCH];   // b', c', r, g
     __shared__ float4 s2[BATCH];   // b, depth, beta, -
@@ -52,6 +53,7 @@ composite_fwd_kernel(const float4* __restrict__ rec, const int32_t* __restrict__
     float T = 1.0f;
     float acc[GSB_CH] = {0.f, 0.f, 0.f, 0.f, 0.f};
     int cur = 0;
+    int visited = 0;   // STATS: pairs this pixel evaluated before it stopped (the work unit P)
 
     for (int b0 = rg.start; b0 < rg.end; b0 += BATCH) {
         // barrier: everyone is past the previous batch; leave when every pixel is saturated
@@ -76,6 +78,7 @@ composite_fwd_kernel(const float4* __restrict__ rec, const int32_t* __restrict__
             float alpha = fminf(ALPHA_MAX, g0.z * fast_ex2(-sigma));
             bool hit = !done && sigma >= 0.f && alpha >= ALPHA_MIN;
             bool touched = false;
+            if (STATS && !done) ++visited;
             if (hit) {
                 float next_T = T * (1.0f - alpha);
                 if (next_T <= T_STOP) {
@@ -112,12 +115,17 @@ composite_fwd_kernel(const float4* __restrict__ rec, const int32_t* __restrict__
         alphas[pix] = 1.0f - T;
         last_ids[pix] = cur;
     }
+    if (STATS) {
+        int v = __reduce_add_sync(0xffffffffu, inside ? visited : 0);
+        if (lane == 0 && v) atomicAdd(pair_count, (unsigned long long)v);
+    }
 }
 
 GSB_API int gsb_composite_fwd(const float* rec, const int32_t* flatten_ids, const int32_t* offsets,
                               const float* backgrounds, int C, int N, int width, int height, int tile_w,
                               int tile_h, int64_t n_isects, float visibility_min_T, float* render,
-                              float* alphas, int32_t* last_ids, int32_t* n_touched, void* stream) {
+                              float* alphas, int32_t* last_ids, int32_t* n_touched,
+                              int64_t* pair_count, void* stream) {
     (void)N;
     GSB_CHECK_ARG(C >= 0 && width > 0 && height > 0 && tile_w > 0 && tile_h > 0);
     if (C == 0) return 0;
@@ -126,14 +134,16 @@ GSB_API int gsb_composite_fwd(const float* rec, const int32_t* flatten_ids, cons
     GSB_CHECK_ARG(n_isects < ((int64_t)1 << 31) && C <= 65535);
     dim3 grid(tile_w, tile_h, C);
     const float4* r4 = reinterpret_cast<const float4*>(rec);
-    if (n_touched)
-        composite_fwd_kernel<true><<<grid, 256, 0, gsb_stream(stream)>>>(
-            r4, flatten_ids, offsets, backgrounds, C, width, height, tile_w, tile_h, n_isects,
-            visibility_min_T, render, alphas, last_ids, n_touched);
-    else
-        composite_fwd_kernel<false><<<grid, 256, 0, gsb_stream(stream)>>>(
-            r4, flatten_ids, offsets, backgrounds, C, width, height, tile_w, tile_h, n_isects,
-            visibility_min_T, render, alphas, last_ids, n_touched);
+    unsigned long long* pc = reinterpret_cast<unsigned long long*>(pair_count);
+#define GSB_FWD(COUNT, STATS)                                                                     \
+    composite_fwd_kernel<COUNT, STATS><<<grid, 256, 0, gsb_stream(stream)>>>(                     \
+        r4, flatten_ids, offsets, backgrounds, C, width, height, tile_w, tile_h, n_isects,        \
+        visibility_min_T, render, alphas, last_ids, n_touched, pc)
+    if (n_touched && pc) GSB_FWD(true, true);
+    else if (n_touched) GSB_FWD(true, false);
+    else if (pc) GSB_FWD(false, true);
+    else GSB_FWD(false, false);
+#undef GSB_FWD
     GSB_LAUNCH_CHECK();
     return 0;
 }

@@ -17,11 +17,14 @@ import torch
 from torch import Tensor
 
 from . import _lib
-from ._lib import check, lib, ptr, stream
+from ._lib import call, check, lib, ptr, stream
 
 REC = 12
 CH = 5
 TILE = 16
+
+# bench.py sets this to a zeroed int64[1] CUDA tensor to collect P (pairs evaluated); None otherwise
+pair_counter: Optional[Tensor] = None
 
 
 def _c(t: Optional[Tensor]) -> Optional[Tensor]:
@@ -50,11 +53,10 @@ class _Project(torch.autograd.Function):
         tiles = torch.empty(C, N, dtype=torch.int32, device=dev)
         means2d = torch.empty(C, N, 2, dtype=torch.float32, device=dev)
         rec = torch.empty(C, N, REC, dtype=torch.float32, device=dev)
-        check(lib().gsb_project_fwd(
+        call("gsb_project_fwd", 
             ptr(means), ptr(quats), ptr(log_scales), ptr(logit_opacities), ptr(logit_colors),
             ptr(log_unc), ptr(viewmats), ptr(Ks), C, N, width, height, eps2d, near_plane, far_plane,
-            radius_clip, tile_w, tile_h, ptr(radii), ptr(means2d), ptr(rec), ptr(tiles), stream()),
-            "gsb_project_fwd")
+            radius_clip, tile_w, tile_h, ptr(radii), ptr(means2d), ptr(rec), ptr(tiles), stream())
         ctx.save_for_backward(means, quats, log_scales, logit_opacities, logit_colors, log_unc,
                               viewmats, Ks, radii, rec)
         ctx.dims = (C, N, width, height, eps2d)
@@ -97,12 +99,11 @@ class _Project(torch.autograd.Function):
             v_means = v_quats = v_scales = v_opac = v_colors = v_unc = None
         v_view = torch.zeros(C, 4, 4, dtype=torch.float32, device=dev) if need_view else None
         if need_gauss or need_view:
-            check(lib().gsb_project_bwd(
+            call("gsb_project_bwd", 
                 ptr(means), ptr(quats), ptr(log_scales), ptr(logit_opacities), ptr(logit_colors),
                 ptr(log_unc), ptr(viewmats), ptr(Ks), C, N, width, height, eps2d, ptr(radii), ptr(rec),
                 ptr(g_means2d), m2_stride, ptr(g_rec), int(need_gauss), ptr(v_means), ptr(v_quats),
-                ptr(v_scales), ptr(v_opac), ptr(v_colors), ptr(v_unc), ptr(v_view), stream()),
-                "gsb_project_bwd")
+                ptr(v_scales), ptr(v_opac), ptr(v_colors), ptr(v_unc), ptr(v_view), stream())
         grads = [v_means, v_quats, v_scales, v_opac, v_colors,
                  v_unc if log_unc is not None else None]
         grads = [g if n else None for g, n in zip(grads, need[:6])]
@@ -123,10 +124,10 @@ class _Composite(torch.autograd.Function):
         alphas = torch.empty(C, height, width, 1, dtype=torch.float32, device=dev)
         last_ids = torch.empty(C, height, width, dtype=torch.int32, device=dev)
         n_touched = torch.zeros(C, N, dtype=torch.int32, device=dev) if count_touched else None
-        check(lib().gsb_composite_fwd(
+        call("gsb_composite_fwd", 
             ptr(rec), ptr(flatten_ids), ptr(offsets), ptr(backgrounds), C, N, width, height, tile_w,
             tile_h, n_isects, visibility_min_T, ptr(render), ptr(alphas), ptr(last_ids),
-            ptr(n_touched), stream()), "gsb_composite_fwd")
+            ptr(n_touched), ptr(pair_counter), stream())
         ctx.save_for_backward(rec, flatten_ids, offsets, backgrounds, alphas, last_ids)
         ctx.dims = (C, N, width, height, tile_w, tile_h)
         if n_touched is None:
@@ -146,10 +147,10 @@ class _Composite(torch.autograd.Function):
         v_rec = torch.zeros(C, N, REC, dtype=torch.float32, device=dev)
         need_bg = backgrounds is not None and ctx.needs_input_grad[4]
         v_bg = torch.zeros(C, CH, dtype=torch.float32, device=dev) if need_bg else None
-        check(lib().gsb_composite_bwd(
+        call("gsb_composite_bwd", 
             ptr(rec), ptr(flatten_ids), ptr(offsets), ptr(backgrounds), C, N, width, height, tile_w,
             tile_h, flatten_ids.numel(), ptr(alphas), ptr(last_ids), ptr(v_render), ptr(v_alphas),
-            ptr(v_rec), ptr(v_bg), stream()), "gsb_composite_bwd")
+            ptr(v_rec), ptr(v_bg), stream())
         # x,y gradients travel on the means2d edge; _Project.backward ignores those two slots of v_rec
         return v_rec, v_rec[..., 0:2], None, None, v_bg, None, None, None, None, None, None
 
@@ -169,8 +170,8 @@ def inclusive_scan(x_i32: Tensor, flag_positive: bool = False) -> Tensor:
     if n:
         nbytes = lib().gsb_scan_workspace_bytes(n)
         ws = _lib.workspace("scan", nbytes, x_i32.device)
-        check(lib().gsb_scan_i32_i64(ptr(x_i32), n, int(flag_positive), ptr(out), ptr(ws), ws.numel(),
-                                     stream()), "gsb_scan_i32_i64")
+        call("gsb_scan_i32_i64", ptr(x_i32), n, int(flag_positive), ptr(out), ptr(ws), ws.numel(),
+                                     stream())
     return out
 
 
@@ -181,7 +182,7 @@ def read_i64(t: Tensor, index: int = -1) -> int:
         return 0
     host = ct.c_int64(0)
     src = t.data_ptr() + (index % t.numel()) * 8
-    check(lib().gsb_read_i64_host(src, ct.addressof(host), stream()), "gsb_read_i64_host")
+    call("gsb_read_i64_host", src, ct.addressof(host), stream())
     return int(host.value)
 
 
@@ -193,8 +194,8 @@ def sort_pairs(keys: Tensor, vals: Tensor, end_bit: int):
     if n:
         nbytes = lib().gsb_sort_workspace_bytes(n)
         ws = _lib.workspace("sort", nbytes, keys.device)
-        check(lib().gsb_sort_pairs(ptr(keys), ptr(vals), ptr(keys_out), ptr(vals_out), n, end_bit,
-                                   ptr(ws), ws.numel(), stream()), "gsb_sort_pairs")
+        call("gsb_sort_pairs", ptr(keys), ptr(vals), ptr(keys_out), ptr(vals_out), n, end_bit,
+                                   ptr(ws), ws.numel(), stream())
     return keys_out, vals_out
 
 
@@ -209,9 +210,8 @@ def isect_tiles(means2d, radii, rec, tiles_per_gauss, tile_w, tile_h, sort=True)
     isect_ids = torch.empty(n_isects, dtype=torch.int64, device=dev)
     flatten_ids = torch.empty(n_isects, dtype=torch.int32, device=dev)
     if n_isects:
-        check(lib().gsb_isect_emit(ptr(means2d), ptr(radii), ptr(rec), ptr(cum), C, N, tile_w, tile_h,
-                                   tile_n_bits, ptr(isect_ids), ptr(flatten_ids), stream()),
-              "gsb_isect_emit")
+        call("gsb_isect_emit", ptr(means2d), ptr(radii), ptr(rec), ptr(cum), C, N, tile_w, tile_h,
+                                   tile_n_bits, ptr(isect_ids), ptr(flatten_ids), stream())
         if sort:
             isect_ids, flatten_ids = sort_pairs(isect_ids, flatten_ids, 32 + tile_n_bits + cam_n_bits)
     return isect_ids, flatten_ids
@@ -222,8 +222,8 @@ def isect_offset_encode(isect_ids, n_cameras, tile_w, tile_h):
     """K5 (reference gslam/rasterization.py:274)."""
     tile_n_bits, _ = tile_bits(tile_w, tile_h, n_cameras)
     offsets = torch.empty(n_cameras, tile_h, tile_w, dtype=torch.int32, device=isect_ids.device)
-    check(lib().gsb_isect_offsets(ptr(isect_ids), isect_ids.numel(), n_cameras, tile_w, tile_h,
-                                  tile_n_bits, ptr(offsets), stream()), "gsb_isect_offsets")
+    call("gsb_isect_offsets", ptr(isect_ids), isect_ids.numel(), n_cameras, tile_w, tile_h,
+                                  tile_n_bits, ptr(offsets), stream())
     return offsets
 
 
@@ -247,7 +247,7 @@ def pack_visible(radii, means2d, rec):
     means2d_out = torch.empty(nnz, 2, dtype=torch.float32, device=dev)
     depths_out = torch.empty(nnz, dtype=torch.float32, device=dev)
     if nnz:
-        check(lib().gsb_pack_visible(ptr(radii), ptr(means2d), ptr(rec), ptr(cum), C, N,
+        call("gsb_pack_visible", ptr(radii), ptr(means2d), ptr(rec), ptr(cum), C, N,
                                      ptr(camera_ids), ptr(gaussian_ids), ptr(radii_out),
-                                     ptr(means2d_out), ptr(depths_out), stream()), "gsb_pack_visible")
+                                     ptr(means2d_out), ptr(depths_out), stream())
     return camera_ids, gaussian_ids, radii_out, means2d_out, depths_out

@@ -105,12 +105,15 @@ int gsb_isect_offsets(const int64_t* isect_ids, int64_t n_isects, int C, int til
 
 /* K6: per-tile front-to-back compositing (reference gslam/rasterization.py:325-339).
  * backgrounds[C,5] may be NULL.  n_touched[C,N] i32 must be zeroed by the caller
- * (NULL skips the count).  Outputs render[C,H,W,5], alphas[C,H,W], last_ids[C,H,W]. */
+ * (NULL skips the count).  Outputs render[C,H,W,5], alphas[C,H,W], last_ids[C,H,W].
+ * pair_count (NULL in the product path) accumulates P, the number of (pixel,
+ * Gaussian) pairs evaluated before each pixel stopped: the work unit of K6/K7
+ * (SURVEY.md 8d); the caller zeroes it. */
 int gsb_composite_fwd(const float* rec, const int32_t* flatten_ids, const int32_t* offsets,
                       const float* backgrounds, int C, int N, int width, int height,
                       int tile_w, int tile_h, int64_t n_isects, float visibility_min_T,
                       float* render, float* alphas, int32_t* last_ids, int32_t* n_touched,
-                      void* stream);
+                      int64_t* pair_count, void* stream);
 
 /* K7: compositing backward.  v_rec[C,N,12] must be zeroed by the caller and is
  * accumulated atomically (x,y slots hold v_means2d).  v_backgrounds[C,5] may be NULL. */
