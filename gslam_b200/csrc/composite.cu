@@ -24,7 +24,8 @@ __device__ __forceinline__ TileRange tile_range(const int32_t* offsets, int cam,
     TileRange r;
     int lin = cam * n_tiles + tile;
     r.start = offsets[lin];
-    r.end = (lin == C * n_tiles - 1) ? (int)n_isects : offsets[lin + 1];
+    // n_isects < 0: offsets has C*T+1 entries (device-side count, gsb_tile_scan)
+    r.end = (lin == C * n_tiles - 1 && n_isects >= 0) ? (int)n_isects : offsets[lin + 1];
     return r;
 }
 
@@ -130,7 +131,7 @@ GSB_API int gsb_composite_fwd(const float* rec, const int32_t* flatten_ids, cons
     GSB_CHECK_ARG(C >= 0 && width > 0 && height > 0 && tile_w > 0 && tile_h > 0);
     if (C == 0) return 0;
     GSB_CHECK_ARG(offsets && render && alphas && last_ids);
-    GSB_CHECK_ARG(n_isects == 0 || (rec && flatten_ids));
+    GSB_CHECK_ARG(n_isects <= 0 || (rec && flatten_ids));
     GSB_CHECK_ARG(n_isects < ((int64_t)1 << 31) && C <= 65535);
     dim3 grid(tile_w, tile_h, C);
     const float4* r4 = reinterpret_cast<const float4*>(rec);

@@ -138,7 +138,7 @@ project_fwd_kernel(const float* __restrict__ means, const float* __restrict__ qu
                    int width, int height, float eps2d, float near_plane, float far_plane,
                    float radius_clip, int tile_w, int tile_h, int32_t* __restrict__ radii,
                    float* __restrict__ means2d, float* __restrict__ rec,
-                   int32_t* __restrict__ tiles_per_gauss) {
+                   int32_t* __restrict__ tiles_per_gauss, int32_t* __restrict__ tile_counts) {
     __shared__ Cam cams[MAX_CAMS_SMEM];
     int n = blockIdx.x * blockDim.x + threadIdx.x;
     float mu[3], q[4], ls[3], Rq[9], s[3], Sig[9], qinv;
@@ -178,6 +178,11 @@ project_fwd_kernel(const float* __restrict__ means, const float* __restrict__ qu
                 int x0, x1, y0, y1;
                 tile_bbox(p.mx, p.my, rad, tile_w, tile_h, x0, x1, y0, y1);
                 cnt = (x1 - x0) * (y1 - y0);
+                if (tile_counts) {
+                    int32_t* tc = tile_counts + (size_t)(c0 + ci) * tile_w * tile_h;
+                    for (int ty = y0; ty < y1; ++ty)
+                        for (int tx = x0; tx < x1; ++tx) atomicAdd(tc + ty * tile_w + tx, 1);
+                }
             }
             radii[idx] = rad;
             tiles_per_gauss[idx] = cnt;
@@ -194,7 +199,7 @@ GSB_API int gsb_project_fwd(const float* means, const float* quats, const float*
                             int N, int width, int height, float eps2d, float near_plane,
                             float far_plane, float radius_clip, int tile_w, int tile_h,
                             int32_t* radii, float* means2d, float* rec, int32_t* tiles_per_gauss,
-                            void* stream) {
+                            int32_t* tile_counts, void* stream) {
     GSB_CHECK_ARG(C >= 0 && N >= 0 && width > 0 && height > 0);
     if (C == 0 || N == 0) return 0;
     GSB_CHECK_ARG(means && quats && log_scales && logit_opacities && logit_colors && viewmats && Ks);
@@ -203,7 +208,7 @@ GSB_API int gsb_project_fwd(const float* means, const float* quats, const float*
     project_fwd_kernel<<<blocks, 256, 0, gsb_stream(stream)>>>(
         means, quats, log_scales, logit_opacities, logit_colors, log_unc, viewmats, Ks, C, N, width,
         height, eps2d, near_plane, far_plane, radius_clip, tile_w, tile_h, radii, means2d, rec,
-        tiles_per_gauss);
+        tiles_per_gauss, tile_counts);
     GSB_LAUNCH_CHECK();
     return 0;
 }

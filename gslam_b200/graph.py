@@ -1,0 +1,52 @@
+"""CUDA-graph capture of a whole fwd+bwd step (launch-bound loops: tracking closure, mapping step).
+
+The only host sync of the eager path is the intersection-count readback that
+sizes the key buffers (upstream gsplat has the same sync inside isect_tiles).
+Under capture the buffers get a fixed capacity instead and the kernels read the
+count from device memory, so the whole step replays with one launch.  If a
+replay ever produces more intersections than the capacity, `overflow` (a device
+flag) is non-zero for that replay and the caller must re-capture with a larger
+capacity; results of an overflowed replay are incomplete.
+"""
+from __future__ import annotations
+
+from typing import Callable
+
+import torch
+
+from . import _lib, ops
+
+
+class GraphedStep:
+    def __init__(self, fn: Callable[[], torch.Tensor], headroom: float = 1.3, warmup: int = 2):
+        """`fn()` runs one full step (forward, loss, backward, collectives) on static tensors
+        and returns the loss.  It is run eagerly `warmup` times (which also measures the
+        intersection count), then captured."""
+        assert ops.isect_capacity is None
+        n_max = 0
+        for _ in range(max(warmup, 1)):
+            fn()
+            n_max = max(n_max, int(ops.last_n_isects.item()))
+        self.capacity = int(n_max * headroom) + 4096
+        torch.cuda.synchronize()
+        self.graph = torch.cuda.CUDAGraph()
+        launches0 = _lib.launch_count
+        ops.isect_capacity = self.capacity
+        try:
+            with torch.cuda.graph(self.graph):
+                self.loss = fn()
+            self.overflow = ops.last_overflow
+            self.n_isects = ops.last_n_isects
+        finally:
+            ops.isect_capacity = None
+        self.launches_per_replay = _lib.launch_count - launches0
+
+    def replay(self) -> torch.Tensor:
+        self.graph.replay()
+        return self.loss
+
+    def check(self) -> None:
+        if int(self.overflow.item()) != 0:
+            raise RuntimeError(
+                f"GraphedStep: {int(self.n_isects.item())} tile intersections exceed the captured "
+                f"capacity {self.capacity}; re-capture with more headroom")

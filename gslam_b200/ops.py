@@ -53,18 +53,20 @@ class _Project(torch.autograd.Function):
         tiles = torch.empty(C, N, dtype=torch.int32, device=dev)
         means2d = torch.empty(C, N, 2, dtype=torch.float32, device=dev)
         rec = torch.empty(C, N, REC, dtype=torch.float32, device=dev)
+        tile_counts = torch.zeros(C, tile_h * tile_w, dtype=torch.int32, device=dev)
         call("gsb_project_fwd", 
             ptr(means), ptr(quats), ptr(log_scales), ptr(logit_opacities), ptr(logit_colors),
             ptr(log_unc), ptr(viewmats), ptr(Ks), C, N, width, height, eps2d, near_plane, far_plane,
-            radius_clip, tile_w, tile_h, ptr(radii), ptr(means2d), ptr(rec), ptr(tiles), stream())
+            radius_clip, tile_w, tile_h, ptr(radii), ptr(means2d), ptr(rec), ptr(tiles),
+            ptr(tile_counts), stream())
         ctx.save_for_backward(means, quats, log_scales, logit_opacities, logit_colors, log_unc,
                               viewmats, Ks, radii, rec)
         ctx.dims = (C, N, width, height, eps2d)
-        ctx.mark_non_differentiable(radii, tiles)
-        return radii, means2d, rec, tiles
+        ctx.mark_non_differentiable(radii, tiles, tile_counts)
+        return radii, means2d, rec, tiles, tile_counts
 
     @staticmethod
-    def backward(ctx, _g_radii, g_means2d, g_rec, _g_tiles):
+    def backward(ctx, _g_radii, g_means2d, g_rec, _g_tiles, _g_counts):
         (means, quats, log_scales, logit_opacities, logit_colors, log_unc, viewmats, Ks, radii,
          rec) = ctx.saved_tensors
         C, N, width, height, eps2d = ctx.dims
@@ -118,7 +120,8 @@ class _Composite(torch.autograd.Function):
         # gradient is delivered as a separate autograd edge.
         C, N = rec.shape[0], rec.shape[1]
         dev = rec.device
-        n_isects = flatten_ids.numel()
+        # offsets with C*T+1 entries carry the intersection count on the device (bin_tiles)
+        n_isects = -1 if offsets.numel() == C * tile_w * tile_h + 1 else flatten_ids.numel()
         backgrounds = _c(backgrounds)
         render = torch.empty(C, height, width, CH, dtype=torch.float32, device=dev)
         alphas = torch.empty(C, height, width, 1, dtype=torch.float32, device=dev)
@@ -129,7 +132,7 @@ class _Composite(torch.autograd.Function):
             tile_h, n_isects, visibility_min_T, ptr(render), ptr(alphas), ptr(last_ids),
             ptr(n_touched), ptr(pair_counter), stream())
         ctx.save_for_backward(rec, flatten_ids, offsets, backgrounds, alphas, last_ids)
-        ctx.dims = (C, N, width, height, tile_w, tile_h)
+        ctx.dims = (C, N, width, height, tile_w, tile_h, n_isects)
         if n_touched is None:
             n_touched = torch.zeros(C, N, dtype=torch.int32, device=dev)
         ctx.mark_non_differentiable(n_touched)
@@ -138,7 +141,7 @@ class _Composite(torch.autograd.Function):
     @staticmethod
     def backward(ctx, v_render, v_alphas, _g_touched):
         rec, flatten_ids, offsets, backgrounds, alphas, last_ids = ctx.saved_tensors
-        C, N, width, height, tile_w, tile_h = ctx.dims
+        C, N, width, height, tile_w, tile_h, n_isects = ctx.dims
         dev = rec.device
         if v_render is None:
             v_render = torch.zeros(C, height, width, CH, dtype=torch.float32, device=dev)
@@ -149,7 +152,7 @@ class _Composite(torch.autograd.Function):
         v_bg = torch.zeros(C, CH, dtype=torch.float32, device=dev) if need_bg else None
         call("gsb_composite_bwd", 
             ptr(rec), ptr(flatten_ids), ptr(offsets), ptr(backgrounds), C, N, width, height, tile_w,
-            tile_h, flatten_ids.numel(), ptr(alphas), ptr(last_ids), ptr(v_render), ptr(v_alphas),
+            tile_h, n_isects, ptr(alphas), ptr(last_ids), ptr(v_render), ptr(v_alphas),
             ptr(v_rec), ptr(v_bg), stream())
         # x,y gradients travel on the means2d edge; _Project.backward ignores those two slots of v_rec
         return v_rec, v_rec[..., 0:2], None, None, v_bg, None, None, None, None, None, None
@@ -225,6 +228,45 @@ def isect_offset_encode(isect_ids, n_cameras, tile_w, tile_h):
     call("gsb_isect_offsets", ptr(isect_ids), isect_ids.numel(), n_cameras, tile_w, tile_h,
                                   tile_n_bits, ptr(offsets), stream())
     return offsets
+
+
+# Capacity mode (no host sync, CUDA-graph capturable): when set, bin_tiles() sizes the key
+# buffers with this many entries instead of reading the intersection count back; the
+# device flag `last_overflow` is non-zero if a call produced more intersections than that.
+isect_capacity: Optional[int] = None
+last_overflow: Optional[Tensor] = None
+last_n_isects: Optional[Tensor] = None
+
+
+@torch.no_grad()
+def bin_tiles(means2d, radii, rec, tile_counts, tile_w, tile_h):
+    """K4+K5, tile-binned (csrc/binning.cu): -> isect_ids, flatten_ids, offsets[C*T+1] i32.
+
+    Bit-identical to isect_tiles(sort=True) + isect_offset_encode.  In the default
+    (strict) mode the intersection count is read back once to size the outputs exactly,
+    like upstream; with `isect_capacity` set nothing synchronises."""
+    global last_overflow, last_n_isects
+    C, N = radii.shape
+    dev = radii.device
+    T = tile_w * tile_h
+    tile_n_bits, _ = tile_bits(tile_w, tile_h, C)
+    offsets = torch.empty(C * T + 1, dtype=torch.int32, device=dev)
+    cursors = torch.empty(C * T, dtype=torch.int32, device=dev)
+    n_dev = torch.empty(1, dtype=torch.int64, device=dev)
+    overflow = torch.zeros(1, dtype=torch.int32, device=dev)
+    call("gsb_tile_scan", ptr(tile_counts), C, tile_w, tile_h, ptr(offsets), ptr(cursors), ptr(n_dev),
+         stream())
+    cap = isect_capacity if isect_capacity is not None else read_i64(n_dev)
+    depth_id = torch.empty(cap, dtype=torch.int64, device=dev)
+    isect_ids = torch.empty(cap, dtype=torch.int64, device=dev)
+    flatten_ids = torch.empty(cap, dtype=torch.int32, device=dev)
+    if cap:
+        call("gsb_isect_scatter", ptr(means2d), ptr(radii), ptr(rec), C, N, tile_w, tile_h, ptr(cursors),
+             cap, ptr(depth_id), ptr(overflow), stream())
+        call("gsb_segment_sort", ptr(depth_id), ptr(offsets), C, tile_w, tile_h, tile_n_bits, cap,
+             ptr(isect_ids), ptr(flatten_ids), stream())
+    last_overflow, last_n_isects = overflow, n_dev
+    return isect_ids, flatten_ids, offsets
 
 
 def composite(rec, means2d, flatten_ids, offsets, backgrounds, width, height, visibility_min_T=0.5,

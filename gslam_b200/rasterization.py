@@ -113,14 +113,15 @@ def rasterization(
     tile_height = math.ceil(height / float(tile_size))
 
     # K8+K1 (+ tile counting): activations, projection and record packing in one kernel
-    radii, means2d, rec, tiles_per_gauss = ops.project(
+    radii, means2d, rec, tiles_per_gauss, tile_counts = ops.project(
         means, quats, log_scales, logit_opacities, logit_colors, log_uncertainties, viewmats, Ks,
         width, height, eps2d, near_plane, far_plane, radius_clip)
 
-    # K4+K5
-    isect_ids, flatten_ids = ops.isect_tiles(means2d, radii, rec, tiles_per_gauss, tile_width,
-                                             tile_height)
-    isect_offsets = ops.isect_offset_encode(isect_ids, C, tile_width, tile_height)
+    # K4+K5: counting sort by tile + per-tile depth sort (bit-identical to the upstream
+    # emit / stable radix sort / offset-encode chain, which ops.isect_tiles still provides)
+    isect_ids, flatten_ids, offsets = ops.bin_tiles(means2d, radii, rec, tile_counts, tile_width,
+                                                    tile_height)
+    isect_offsets = offsets[:-1].view(C, tile_height, tile_width)
 
     # backgrounds [C,3] -> [C,5] = (r, g, b, 0, e)   (reference :236-255)
     bg5 = None
@@ -132,7 +133,7 @@ def rasterization(
             bg5[:, 4] = math.e
 
     # K6
-    render, alphas, n_touched = ops.composite(rec, means2d, flatten_ids, isect_offsets, bg5, width,
+    render, alphas, n_touched = ops.composite(rec, means2d, flatten_ids, offsets, bg5, width,
                                               height, visibility_min_T)
 
     out = RasterizationOutput(
@@ -187,7 +188,7 @@ def get_new_splat_depth(
     N = means.shape[0]
     zeros = torch.zeros(N, dtype=torch.float32, device=means.device)
     with torch.no_grad():
-        radii, means2d, rec, _ = ops.project(
+        radii, means2d, rec, _, _ = ops.project(
             means, quats, log_scales, zeros, zeros[:, None].expand(N, 3), None, viewmats, Ks,
             width, height, eps2d, near_plane, far_plane, radius_clip)
         if packed:

@@ -45,14 +45,16 @@ int gsb_read_i64_host(const int64_t* src, int64_t* dst_host, void* stream);
 /* K1+K8: activations + EWA projection + tile counting, unpacked.
  * Replaces gslam/rasterization.py:145-170, :187, :225-256 and the counting
  * half of isect_tiles (:261).  log_unc may be NULL (beta record slot = 0).
- * Outputs: radii[C,N] i32, means2d[C,N,2], rec[C,N,12], tiles_per_gauss[C,N] i32. */
+ * Outputs: radii[C,N] i32, means2d[C,N,2], rec[C,N,12], tiles_per_gauss[C,N] i32.
+ * tile_counts[C, tile_h*tile_w] i32 (may be NULL; zeroed by the caller) receives the
+ * number of intersections per (camera, tile) for the tile-binned sort below. */
 int gsb_project_fwd(const float* means, const float* quats, const float* log_scales,
                     const float* logit_opacities, const float* logit_colors,
                     const float* log_unc, const float* viewmats, const float* Ks,
                     int C, int N, int width, int height, float eps2d, float near_plane,
                     float far_plane, float radius_clip, int tile_w, int tile_h,
                     int32_t* radii, float* means2d, float* rec, int32_t* tiles_per_gauss,
-                    void* stream);
+                    int32_t* tile_counts, void* stream);
 
 /* K2+K8 backward.  v_rec[C,N,12] carries the gradients of every record slot
  * except x,y, which come from v_means2d (element stride `v_means2d_stride`
@@ -99,11 +101,30 @@ int gsb_sort_pairs(int64_t* keys_in, int32_t* vals_in, int64_t* keys_out, int32_
                    int64_t n, int end_bit, void* workspace, size_t workspace_bytes,
                    void* stream);
 
+/* K4+K5, tile-binned form (the product path; bit-identical to emit + stable sort +
+ * offset encode, see csrc/binning.cu).  No step needs the intersection count I on
+ * the host: it is offsets[C*T] (and *n_isects).
+ *   gsb_tile_scan    : exclusive scan of tile_counts -> offsets[C*T+1] i32, cursors[C*T] i32
+ *   gsb_isect_scatter: (depth bits << 32 | flatten_id) into each tile's segment of
+ *                      depth_id[capacity]; sets *overflow when I > capacity
+ *   gsb_segment_sort : sorts every segment in shared memory and writes
+ *                      isect_ids[capacity] i64, flatten_ids[capacity] i32 */
+int gsb_tile_scan(const int32_t* tile_counts, int C, int tile_w, int tile_h, int32_t* offsets,
+                  int32_t* cursors, int64_t* n_isects, void* stream);
+int gsb_isect_scatter(const float* means2d, const int32_t* radii, const float* rec, int C, int N,
+                      int tile_w, int tile_h, int32_t* cursors, int64_t capacity,
+                      int64_t* depth_id, int32_t* overflow, void* stream);
+int gsb_segment_sort(int64_t* depth_id, const int32_t* offsets, int C, int tile_w, int tile_h,
+                     int tile_n_bits, int64_t capacity, int64_t* isect_ids,
+                     int32_t* flatten_ids, void* stream);
+
 /* K5: isect_offset_encode (reference gslam/rasterization.py:274). */
 int gsb_isect_offsets(const int64_t* isect_ids, int64_t n_isects, int C, int tile_w,
                       int tile_h, int tile_n_bits, int32_t* offsets, void* stream);
 
 /* K6: per-tile front-to-back compositing (reference gslam/rasterization.py:325-339).
+ * offsets holds C*T entries and n_isects closes the last tile; pass n_isects < 0 when
+ * offsets has C*T+1 entries (gsb_tile_scan), so that no host-side count is needed.
  * backgrounds[C,5] may be NULL.  n_touched[C,N] i32 must be zeroed by the caller
  * (NULL skips the count).  Outputs render[C,H,W,5], alphas[C,H,W], last_ids[C,H,W].
  * pair_count (NULL in the product path) accumulates P, the number of (pixel,

@@ -43,7 +43,7 @@ def gpu_project(sc, dev):
 def test_projection_forward(cuda, n, c, scale):
     sc = make_scene(n, c, "tum", scale)
     radii, m2, d, con, opac, colors, betas = oracle_projection(sc)
-    g_radii, g_m2, g_rec, g_tiles = gpu_project(sc, cuda)
+    g_radii, g_m2, g_rec, g_tiles, g_counts = gpu_project(sc, cuda)
     g_radii, g_m2, g_rec, g_tiles = g_radii.cpu(), g_m2.cpu(), g_rec.cpu(), g_tiles.cpu()
     # radii may differ by one where 3*sqrt(lambda) lands within an ulp of an integer
     same = g_radii == radii
@@ -61,15 +61,16 @@ def test_projection_forward(cuda, n, c, scale):
     th, tw = math.ceil(sc.height / 16), math.ceil(sc.width / 16)
     tiles_ref, _, _ = R.isect_tiles(g_m2, g_radii, g_rec[..., 9], 16, tw, th, sort=False)
     assert torch.equal(g_tiles, tiles_ref)
+    assert int(g_counts.sum()) == int(tiles_ref.sum())
 
 
 @pytest.mark.parametrize("n,c,scale", [(4000, 1, 0.5), (1500, 4, 0.25), (0, 1, 0.25), (5, 9, 0.25)])
 def test_isect_bit_exact(cuda, n, c, scale):
     """Counts, sorted keys, values and tile ranges are bit-exact on identical projected inputs."""
     sc = make_scene(max(n, 1), c, "tum", scale)
-    g_radii, g_m2, g_rec, g_tiles = gpu_project(sc, cuda)
+    g_radii, g_m2, g_rec, g_tiles, g_counts = gpu_project(sc, cuda)
     if n == 0:
-        g_radii.zero_(); g_tiles.zero_()
+        g_radii.zero_(); g_tiles.zero_(); g_counts.zero_()
     th, tw = math.ceil(sc.height / 16), math.ceil(sc.width / 16)
     ids, fids = ops.isect_tiles(g_m2, g_radii, g_rec, g_tiles, tw, th)
     offs = ops.isect_offset_encode(ids, c, tw, th)
@@ -83,6 +84,35 @@ def test_isect_bit_exact(cuda, n, c, scale):
     ids_u, fids_u = ops.isect_tiles(g_m2, g_radii, g_rec, g_tiles, tw, th, sort=False)
     _, ids_ur, fids_ur = R.isect_tiles(g_m2.cpu(), g_radii.cpu(), g_rec[..., 9].cpu(), 16, tw, th, sort=False)
     assert torch.equal(ids_u.cpu(), ids_ur) and torch.equal(fids_u.cpu(), fids_ur)
+    # the tile-binned product path (counting sort + per-tile shared-memory sort) gives the same bits
+    ids_b, fids_b, offs_b = ops.bin_tiles(g_m2, g_radii, g_rec, g_counts, tw, th)
+    assert torch.equal(ids_b.cpu(), ids_ref) and torch.equal(fids_b.cpu(), fids_ref)
+    assert torch.equal(offs_b[:-1].cpu().view(c, th, tw), offs_ref)
+    assert int(offs_b[-1]) == ids_ref.numel()
+    assert int(ops.last_overflow.item()) == 0
+
+
+def test_bin_tiles_long_segments_and_capacity(cuda):
+    """Segments longer than the 8192-entry shared-memory sort, and the no-sync capacity mode."""
+    sc = make_scene(30000, 1, "tum", 0.1, log_scale_mean=math.log(0.05))   # 64x48 px: 12 tiles, huge splats
+    g_radii, g_m2, g_rec, g_tiles, g_counts = gpu_project(sc, cuda)
+    th, tw = math.ceil(sc.height / 16), math.ceil(sc.width / 16)
+    _, ids_ref, fids_ref = R.isect_tiles(g_m2.cpu(), g_radii.cpu(), g_rec[..., 9].cpu(), 16, tw, th)
+    assert int(g_counts.max()) > 8192
+    ids_b, fids_b, offs_b = ops.bin_tiles(g_m2, g_radii, g_rec, g_counts, tw, th)
+    assert torch.equal(ids_b.cpu(), ids_ref) and torch.equal(fids_b.cpu(), fids_ref)
+    I = ids_ref.numel()
+    try:
+        ops.isect_capacity = I + 1000
+        ids_c, fids_c, offs_c = ops.bin_tiles(g_m2, g_radii, g_rec, g_counts, tw, th)
+        assert ids_c.numel() == I + 1000 and int(ops.last_overflow.item()) == 0
+        assert int(ops.last_n_isects.item()) == I
+        assert torch.equal(ids_c[:I].cpu(), ids_ref) and torch.equal(fids_c[:I].cpu(), fids_ref)
+        ops.isect_capacity = I // 2
+        ops.bin_tiles(g_m2, g_radii, g_rec, g_counts, tw, th)
+        assert int(ops.last_overflow.item()) == 1
+    finally:
+        ops.isect_capacity = None
 
 
 def test_sort_random_keys_stable(cuda):
