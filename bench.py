@@ -324,6 +324,9 @@ def run_ours(args):
             "gsb_isect_emit": 16 * CN + 12 * I,
             "gsb_sort_pairs": (24 * 6 + 0) * I,
             "gsb_isect_offsets": 8 * I + 4 * 1200,
+            "gsb_tile_scan": 12 * 1200,
+            "gsb_isect_scatter": 16 * CN + 8 * I,
+            "gsb_segment_sort": (8 + 8 + 4) * I,
             "gsb_composite_fwd": 52 * I + (4 * 5 + 8) * px,
             "gsb_composite_bwd": 52 * I + (8 * 5 + 12) * px + 48 * I,
         }

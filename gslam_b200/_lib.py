@@ -30,7 +30,7 @@ SIGNATURES = {
     "gsb_project_fwd": (_i, [_p] * 8 + [_i, _i, _i, _i, _f, _f, _f, _f, _i, _i] + [_p] * 5 + [_p]),
     "gsb_tile_scan": (_i, [_p, _i, _i, _i, _p, _p, _p, _p]),
     "gsb_isect_scatter": (_i, [_p, _p, _p, _i, _i, _i, _i, _p, _l, _p, _p, _p]),
-    "gsb_segment_sort": (_i, [_p, _p, _i, _i, _i, _i, _l, _p, _p, _p]),
+    "gsb_segment_sort": (_i, [_p, _p, _p, _i, _i, _i, _i, _l, _p, _p, _p]),
     "gsb_project_bwd": (_i, [_p] * 8 + [_i, _i, _i, _i, _f] + [_p, _p, _p, _l, _p, _i] + [_p] * 7 + [_p]),
     "gsb_pack_visible": (_i, [_p] * 4 + [_i, _i] + [_p] * 5 + [_p]),
     "gsb_scan_workspace_bytes": (_z, [_l]),

@@ -27,7 +27,7 @@ tile_scan_kernel(const int32_t* __restrict__ counts, int n, int32_t* __restrict_
     __syncthreads();
     for (int base = 0; base < n; base += 1024) {
         int i = base + tid;
-        int v = (i < n) ? counts[i] : 0;
+        int v = (i < n) ? counts[(size_t)i * GSB_CSTRIDE] : 0;
         int x = v;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
@@ -48,7 +48,7 @@ tile_scan_kernel(const int32_t* __restrict__ counts, int n, int32_t* __restrict_
         __syncthreads();
         int carry = carry_s;
         int excl = carry + (warp ? warp_tot[warp - 1] : 0) + x - v;
-        if (i < n) { offsets[i] = excl; cursors[i] = excl; }
+        if (i < n) { offsets[i] = excl; cursors[(size_t)i * GSB_CSTRIDE] = excl; }
         __syncthreads();
         if (tid == 1023) carry_s = carry + warp_tot[31];
         __syncthreads();
@@ -78,21 +78,29 @@ isect_scatter_kernel(const float* __restrict__ means2d, const int32_t* __restric
                      int32_t* __restrict__ cursors, int64_t capacity, uint64_t* __restrict__ dk,
                      int32_t* __restrict__ overflow) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= CN) return;
-    int r = radii[i];
-    if (r <= 0) return;
-    float2 m = reinterpret_cast<const float2*>(means2d)[i];
-    int x0, x1, y0, y1;
-    tile_bbox(m.x, m.y, r, tile_w, tile_h, x0, x1, y0, y1);
-    int cam = (int)(i / N);
-    uint64_t word = ((uint64_t)__float_as_uint(rec[i * GSB_REC + 9]) << 32) | (uint32_t)i;
-    int32_t* cur = cursors + (size_t)cam * tile_w * tile_h;
-    for (int ty = y0; ty < y1; ++ty)
-        for (int tx = x0; tx < x1; ++tx) {
-            int pos = atomicAdd(cur + ty * tile_w + tx, 1);
-            if (pos < capacity) dk[pos] = word;
+    // a warp never straddles two cameras when N % 32 == 0; otherwise each lane keeps its own camera
+    int r = (i < CN) ? radii[i] : 0;
+    int x0 = 0, x1 = 0, y0 = 0, y1 = 0, cnt = 0, cam = 0;
+    uint32_t dbits = 0;
+    if (r > 0) {
+        float2 m = reinterpret_cast<const float2*>(means2d)[i];
+        tile_bbox(m.x, m.y, r, tile_w, tile_h, x0, x1, y0, y1);
+        cnt = (x1 - x0) * (y1 - y0);
+        cam = (int)(i / N);
+        dbits = __float_as_uint(rec[i * GSB_REC + 9]);
+    }
+    const int n_tiles = tile_w * tile_h;
+    const uint32_t id = (uint32_t)i;
+    warp_expand_tiles(x0, y0, x1 - x0, cnt, [&](int owner, int tx, int ty, bool active) {
+        uint32_t o_d = __shfl_sync(0xffffffffu, dbits, owner);
+        uint32_t o_id = __shfl_sync(0xffffffffu, id, owner);
+        int o_cam = __shfl_sync(0xffffffffu, cam, owner);
+        if (active) {
+            int pos = atomicAdd(cursors + ((size_t)o_cam * n_tiles + ty * tile_w + tx) * GSB_CSTRIDE, 1);
+            if (pos < capacity) dk[pos] = ((uint64_t)o_d << 32) | o_id;
             else *overflow = 1;
         }
+    });
 }
 
 GSB_API int gsb_isect_scatter(const float* means2d, const int32_t* radii, const float* rec, int C, int N,
@@ -112,30 +120,45 @@ GSB_API int gsb_isect_scatter(const float* means2d, const int32_t* radii, const 
 }
 
 // ---------------------------------------------------------------------------
-// per-tile segment sort (bitonic network with all compare-exchanges ascending,
-// so a non-power-of-two length needs no padding: out-of-range partners are +inf)
+// per-tile segment sort.
+//
+// Keys are (depth bits << 32 | flatten_id).  Depth bits of positive floats are
+// monotone in depth, so one CTA per tile does a bucket sort: min/max of the
+// depth bits, a monotone linear map of every key to one of B ~ L buckets
+// (shared-memory counters), an exclusive scan, a scatter, and a tiny insertion
+// sort per bucket (about one key per bucket on average).  Buckets that stay
+// large (equal or tightly clustered depths) are finished by a CTA-wide bitonic
+// network.  Segments up to SEG_SMEM_ELEMS keys are staged in shared memory;
+// longer ones run the same code through L2 with the counters still in shared
+// memory.  O(L) work instead of the O(L log^2 L) of a pure bitonic sort.
 // ---------------------------------------------------------------------------
 #define SEG_THREADS 256
-#define SEG_SMEM_ELEMS 8192   // 64 KB of shared memory; longer segments sort in global memory
+#define SEG_SMEM_ELEMS 2048      // keys staged in shared memory (2 x 16 KB)
+#define SEG_MAX_BUCKETS 4096     // counters: 2 x 16 KB when the key staging area is not used
+#define SEG_SMALL 24             // buckets up to this size are insertion-sorted by one thread
+#define SEG_MAX_BIG 64
+#define SEG_SMEM_BYTES (2 * SEG_MAX_BUCKETS * 4 + 2 * SEG_SMEM_ELEMS * 8)
 
-template <typename Ptr>
-__device__ __forceinline__ void bitonic_sort(Ptr a, int L) {
-    int n2 = 1;
-    while (n2 < L) n2 <<= 1;
-    for (int k = 2; k <= n2; k <<= 1) {
-        // first step of the merge: partner mirrors inside the block of size k
-        for (int t = threadIdx.x; t < n2 / 2; t += SEG_THREADS) {
-            int blk = t / (k / 2), off = t % (k / 2);
-            int i = blk * k + off, p = blk * k + (k - 1 - off);
+// all compare-exchanges ascending, so a non-power-of-two length needs no padding
+// (out-of-range partners act as +inf)
+__device__ __forceinline__ void bitonic_sort(uint64_t* a, int L) {
+    int lg = 0;
+    while ((1 << lg) < L) ++lg;
+    const int half = (1 << lg) >> 1;
+    for (int lk = 1; lk <= lg; ++lk) {
+        const int hk = lk - 1;
+        for (int t = threadIdx.x; t < half; t += SEG_THREADS) {
+            int blk = t >> hk, off = t & ((1 << hk) - 1);
+            int i = (blk << lk) + off, p = (blk << lk) + ((1 << lk) - 1 - off);
             if (p < L) {
                 uint64_t x = a[i], y = a[p];
                 if (x > y) { a[i] = y; a[p] = x; }
             }
         }
         __syncthreads();
-        for (int j = k >> 2; j > 0; j >>= 1) {
-            for (int t = threadIdx.x; t < n2 / 2; t += SEG_THREADS) {
-                int i = ((t / j) * 2 * j) + (t % j), p = i + j;
+        for (int lj = hk - 1; lj >= 0; --lj) {
+            for (int t = threadIdx.x; t < half; t += SEG_THREADS) {
+                int i = ((t >> lj) << (lj + 1)) + (t & ((1 << lj) - 1)), p = i + (1 << lj);
                 if (p < L) {
                     uint64_t x = a[i], y = a[p];
                     if (x > y) { a[i] = y; a[p] = x; }
@@ -146,56 +169,151 @@ __device__ __forceinline__ void bitonic_sort(Ptr a, int L) {
     }
 }
 
+// Sorts in[0..L) into out[0..L).  cnt / fill: B ints each in shared memory.
+__device__ __forceinline__ void bucket_sort(const uint64_t* in, uint64_t* out, int L, int* cnt,
+                                            int* fill) {
+    __shared__ uint32_t red_mn[SEG_THREADS / 32], red_mx[SEG_THREADS / 32];
+    __shared__ int warp_sum_s[SEG_THREADS / 32];
+    __shared__ int big[SEG_MAX_BIG];
+    __shared__ int n_big;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    int lgB = 0;
+    while ((1 << lgB) < L && (1 << lgB) < SEG_MAX_BUCKETS) ++lgB;
+    const int B = 1 << lgB;
+    // 1. depth range
+    uint32_t mn = 0xffffffffu, mx = 0u;
+    for (int t = tid; t < L; t += SEG_THREADS) {
+        uint32_t d = (uint32_t)(in[t] >> 32);
+        mn = min(mn, d); mx = max(mx, d);
+    }
+    mn = __reduce_min_sync(0xffffffffu, mn);
+    mx = __reduce_max_sync(0xffffffffu, mx);
+    if (lane == 0) { red_mn[warp] = mn; red_mx[warp] = mx; }
+    for (int t = tid; t < B; t += SEG_THREADS) { cnt[t] = 0; fill[t] = 0; }
+    if (tid == 0) n_big = 0;
+    __syncthreads();
+#pragma unroll
+    for (int w = 0; w < SEG_THREADS / 32; ++w) { mn = min(mn, red_mn[w]); mx = max(mx, red_mx[w]); }
+    const float scale = (float)B / ((float)(mx - mn) + 1.0f);
+    // 2. histogram
+    for (int t = tid; t < L; t += SEG_THREADS) {
+        uint32_t d = (uint32_t)(in[t] >> 32);
+        int bkt = min(B - 1, (int)((float)(d - mn) * scale));
+        atomicAdd(&cnt[bkt], 1);
+    }
+    __syncthreads();
+    // 3. exclusive scan of cnt (B / 256 consecutive counters per thread), in place
+    {
+        const int per = max(B / SEG_THREADS, 1);
+        const int b0 = tid * per;
+        int local = 0;
+        if (b0 < B)
+            for (int k = 0; k < per; ++k) local += cnt[b0 + k];
+        int x = local;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            int y = __shfl_up_sync(0xffffffffu, x, o);
+            if (lane >= o) x += y;
+        }
+        if (lane == 31) warp_sum_s[warp] = x;
+        __syncthreads();
+        int base = 0;
+        for (int w = 0; w < warp; ++w) base += warp_sum_s[w];
+        int run = base + x - local;
+        if (b0 < B)
+            for (int k = 0; k < per; ++k) {
+                int c = cnt[b0 + k];
+                cnt[b0 + k] = run;
+                run += c;
+            }
+    }
+    __syncthreads();
+    // 4. scatter into buckets
+    for (int t = tid; t < L; t += SEG_THREADS) {
+        uint64_t key = in[t];
+        uint32_t d = (uint32_t)(key >> 32);
+        int bkt = min(B - 1, (int)((float)(d - mn) * scale));
+        int pos = cnt[bkt] + atomicAdd(&fill[bkt], 1);
+        out[pos] = key;
+    }
+    __syncthreads();
+    // 5. finish the buckets
+    for (int bkt = tid; bkt < B; bkt += SEG_THREADS) {
+        int s0 = cnt[bkt], m = fill[bkt];
+        if (m < 2) continue;
+        bool small = m <= SEG_SMALL;
+        if (!small) {
+            int slot = atomicAdd(&n_big, 1);
+            if (slot < SEG_MAX_BIG) big[slot] = bkt;
+            else small = true;          // list full: slow but correct
+        }
+        if (small) {
+            for (int i = 1; i < m; ++i) {
+                uint64_t key = out[s0 + i];
+                int j = i - 1;
+                while (j >= 0 && out[s0 + j] > key) { out[s0 + j + 1] = out[s0 + j]; --j; }
+                out[s0 + j + 1] = key;
+            }
+        }
+    }
+    __syncthreads();
+    const int nb = min(n_big, SEG_MAX_BIG);
+    for (int k = 0; k < nb; ++k) bitonic_sort(out + cnt[big[k]], fill[big[k]]);
+}
+
 __global__ void __launch_bounds__(SEG_THREADS)
-segment_sort_kernel(uint64_t* __restrict__ dk, const int32_t* __restrict__ offsets, int n_tiles,
-                    int tile_n_bits, int64_t capacity, int64_t* __restrict__ isect_ids,
-                    int32_t* __restrict__ flatten_ids) {
-    extern __shared__ uint64_t sm[];
+segment_sort_kernel(uint64_t* __restrict__ dk, uint64_t* __restrict__ tmp,
+                    const int32_t* __restrict__ offsets, int n_tiles, int tile_n_bits, int64_t capacity,
+                    int64_t* __restrict__ isect_ids, int32_t* __restrict__ flatten_ids) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    int* cnt = reinterpret_cast<int*>(smem_raw);
+    int* fill = cnt + SEG_MAX_BUCKETS;
+    uint64_t* sa = reinterpret_cast<uint64_t*>(fill + SEG_MAX_BUCKETS);
+    uint64_t* sb = sa + SEG_SMEM_ELEMS;
     const int lin = blockIdx.x;                 // camera * n_tiles + tile
     int64_t s = offsets[lin], e = offsets[lin + 1];
     if (e > capacity) e = capacity;
     if (s >= e) return;
     const int L = (int)(e - s);
-    uint64_t* seg = dk + s;
     const int cam = lin / n_tiles, tile = lin % n_tiles;
     const int64_t hi = (((int64_t)cam << tile_n_bits) | tile) << 32;
-    if (L <= SEG_SMEM_ELEMS) {
-        for (int t = threadIdx.x; t < L; t += SEG_THREADS) sm[t] = seg[t];
+    const uint64_t* sorted;
+    if (L == 1) {
+        sorted = dk + s;
+    } else if (L <= SEG_SMEM_ELEMS) {
+        for (int t = threadIdx.x; t < L; t += SEG_THREADS) sa[t] = dk[s + t];
         __syncthreads();
-        if (L > 1) bitonic_sort(sm, L);
-        for (int t = threadIdx.x; t < L; t += SEG_THREADS) {
-            uint64_t w = sm[t];
-            isect_ids[s + t] = hi | (int64_t)(w >> 32);
-            flatten_ids[s + t] = (int32_t)(uint32_t)w;
-        }
+        bucket_sort(sa, sb, L, cnt, fill);
+        sorted = sb;
     } else {
-        bitonic_sort(seg, L);    // same network through L2; rare (a tile with > 8192 splats)
-        for (int t = threadIdx.x; t < L; t += SEG_THREADS) {
-            uint64_t w = seg[t];
-            isect_ids[s + t] = hi | (int64_t)(w >> 32);
-            flatten_ids[s + t] = (int32_t)(uint32_t)w;
-        }
+        bucket_sort(dk + s, tmp + s, L, cnt, fill);
+        sorted = tmp + s;
+    }
+    __syncthreads();
+    for (int t = threadIdx.x; t < L; t += SEG_THREADS) {
+        uint64_t w = sorted[t];
+        isect_ids[s + t] = hi | (int64_t)(w >> 32);
+        flatten_ids[s + t] = (int32_t)(uint32_t)w;
     }
 }
 
-GSB_API int gsb_segment_sort(int64_t* depth_id, const int32_t* offsets, int C, int tile_w, int tile_h,
-                             int tile_n_bits, int64_t capacity, int64_t* isect_ids,
-                             int32_t* flatten_ids, void* stream) {
+GSB_API int gsb_segment_sort(int64_t* depth_id, int64_t* scratch, const int32_t* offsets, int C,
+                             int tile_w, int tile_h, int tile_n_bits, int64_t capacity,
+                             int64_t* isect_ids, int32_t* flatten_ids, void* stream) {
     int n = C * tile_w * tile_h;
     if (n == 0 || capacity == 0) return 0;
-    GSB_CHECK_ARG(depth_id && offsets && isect_ids && flatten_ids);
+    GSB_CHECK_ARG(depth_id && scratch && offsets && isect_ids && flatten_ids);
     static bool attr_set[64] = {false};
-    size_t smem = SEG_SMEM_ELEMS * sizeof(uint64_t);
     int dev = 0;
     GSB_CUDA(cudaGetDevice(&dev));
     if (dev >= 64 || !attr_set[dev]) {   // the opt-in above 48 KB is a per-device attribute
         GSB_CUDA(cudaFuncSetAttribute(segment_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      (int)smem));
+                                      SEG_SMEM_BYTES));
         if (dev < 64) attr_set[dev] = true;
     }
-    segment_sort_kernel<<<n, SEG_THREADS, smem, gsb_stream(stream)>>>(
-        reinterpret_cast<uint64_t*>(depth_id), offsets, tile_w * tile_h, tile_n_bits, capacity, isect_ids,
-        flatten_ids);
+    segment_sort_kernel<<<n, SEG_THREADS, SEG_SMEM_BYTES, gsb_stream(stream)>>>(
+        reinterpret_cast<uint64_t*>(depth_id), reinterpret_cast<uint64_t*>(scratch), offsets,
+        tile_w * tile_h, tile_n_bits, capacity, isect_ids, flatten_ids);
     GSB_LAUNCH_CHECK();
     return 0;
 }

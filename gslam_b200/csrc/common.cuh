@@ -57,3 +57,41 @@ __device__ __forceinline__ void tile_bbox(float mx, float my, int radius, int ti
     y0 = min(max(0, (int)floorf(ty - tr)), tile_h);
     y1 = min(max(0, (int)ceilf(ty + tr)), tile_h);
 }
+
+// Warp-balanced expansion of per-lane tile rectangles.  Every lane of a full warp
+// brings a rectangle (x0, y0, width bw, cnt = bw*bh tiles, cnt may be 0); the
+// warp's total work is dealt out one tile per lane per round, so one large splat
+// cannot serialise its lane.  f(owner_lane, tx, ty, active) is called by ALL
+// lanes each round (so it may shuffle from owner_lane); only `active` lanes own
+// a tile.
+template <typename F>
+__device__ __forceinline__ void warp_expand_tiles(int x0, int y0, int bw, int cnt, F&& f) {
+    const unsigned full = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    int incl = cnt;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        int y = __shfl_up_sync(full, incl, o);
+        if (lane >= o) incl += y;
+    }
+    const int total = __shfl_sync(full, incl, 31);
+    const int excl = incl - cnt;
+    for (int base = 0; base < total; base += 32) {
+        const int k = base + lane;
+        const bool active = k < total;
+        // owner = last lane whose exclusive prefix is <= k (binary search over lanes)
+        int lo = 0;
+#pragma unroll
+        for (int step = 16; step > 0; step >>= 1) {
+            int probe = __shfl_sync(full, excl, lo + step);
+            if (probe <= k) lo += step;
+        }
+        const int o_excl = __shfl_sync(full, excl, lo);
+        const int o_x0 = __shfl_sync(full, x0, lo);
+        const int o_y0 = __shfl_sync(full, y0, lo);
+        const int o_bw = max(__shfl_sync(full, bw, lo), 1);
+        const int local = active ? k - o_excl : 0;
+        const int dy = local / o_bw;
+        f(lo, o_x0 + (local - dy * o_bw), o_y0 + dy, active);
+    }
+}

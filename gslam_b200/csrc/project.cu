@@ -160,13 +160,14 @@ project_fwd_kernel(const float* __restrict__ means, const float* __restrict__ qu
         __syncthreads();
         load_cams(cams, viewmats, Ks, c0, nc);
         __syncthreads();
-        if (n >= N) continue;
         for (int ci = 0; ci < nc; ++ci) {
             size_t idx = (size_t)(c0 + ci) * N + n;
             Proj p;
-            project_one(cams[ci], mu, Sig, width, height, eps2d, near_plane, far_plane, radius_clip, p);
+            p.ok = false;
+            if (n < N)
+                project_one(cams[ci], mu, Sig, width, height, eps2d, near_plane, far_plane, radius_clip, p);
             float4 r0 = make_float4(0.f, 0.f, 0.f, 0.f), r1 = r0, r2 = r0;
-            int rad = 0, cnt = 0;
+            int rad = 0, cnt = 0, x0 = 0, x1 = 0, y0 = 0, y1 = 0;
             float2 m2 = make_float2(0.f, 0.f);
             if (p.ok) {
                 float idet = 1.0f / p.det;
@@ -175,20 +176,22 @@ project_fwd_kernel(const float* __restrict__ means, const float* __restrict__ qu
                 r0 = make_float4(p.mx, p.my, opac, p.c11 * idet);
                 r1 = make_float4(-p.c01 * idet, p.c00 * idet, col[0], col[1]);
                 r2 = make_float4(col[2], p.z, beta, 0.f);
-                int x0, x1, y0, y1;
                 tile_bbox(p.mx, p.my, rad, tile_w, tile_h, x0, x1, y0, y1);
                 cnt = (x1 - x0) * (y1 - y0);
-                if (tile_counts) {
-                    int32_t* tc = tile_counts + (size_t)(c0 + ci) * tile_w * tile_h;
-                    for (int ty = y0; ty < y1; ++ty)
-                        for (int tx = x0; tx < x1; ++tx) atomicAdd(tc + ty * tile_w + tx, 1);
-                }
             }
-            radii[idx] = rad;
-            tiles_per_gauss[idx] = cnt;
-            reinterpret_cast<float2*>(means2d)[idx] = m2;
-            float4* rp = reinterpret_cast<float4*>(rec) + idx * 3;
-            rp[0] = r0; rp[1] = r1; rp[2] = r2;
+            if (n < N) {
+                radii[idx] = rad;
+                tiles_per_gauss[idx] = cnt;
+                reinterpret_cast<float2*>(means2d)[idx] = m2;
+                float4* rp = reinterpret_cast<float4*>(rec) + idx * 3;
+                rp[0] = r0; rp[1] = r1; rp[2] = r2;
+            }
+            if (tile_counts) {
+                int32_t* tc = tile_counts + (size_t)(c0 + ci) * tile_w * tile_h * GSB_CSTRIDE;
+                warp_expand_tiles(x0, y0, x1 - x0, cnt, [&](int, int tx, int ty, bool active) {
+                    if (active) atomicAdd(tc + (size_t)(ty * tile_w + tx) * GSB_CSTRIDE, 1);
+                });
+            }
         }
     }
 }

@@ -22,6 +22,7 @@ from ._lib import call, check, lib, ptr, stream
 REC = 12
 CH = 5
 TILE = 16
+CSTRIDE = 32   # GSB_CSTRIDE: one per-tile counter per 128-byte line
 
 # bench.py sets this to a zeroed int64[1] CUDA tensor to collect P (pairs evaluated); None otherwise
 pair_counter: Optional[Tensor] = None
@@ -53,7 +54,7 @@ class _Project(torch.autograd.Function):
         tiles = torch.empty(C, N, dtype=torch.int32, device=dev)
         means2d = torch.empty(C, N, 2, dtype=torch.float32, device=dev)
         rec = torch.empty(C, N, REC, dtype=torch.float32, device=dev)
-        tile_counts = torch.zeros(C, tile_h * tile_w, dtype=torch.int32, device=dev)
+        tile_counts = torch.zeros(C, tile_h * tile_w, CSTRIDE, dtype=torch.int32, device=dev)
         call("gsb_project_fwd", 
             ptr(means), ptr(quats), ptr(log_scales), ptr(logit_opacities), ptr(logit_colors),
             ptr(log_unc), ptr(viewmats), ptr(Ks), C, N, width, height, eps2d, near_plane, far_plane,
@@ -251,7 +252,7 @@ def bin_tiles(means2d, radii, rec, tile_counts, tile_w, tile_h):
     T = tile_w * tile_h
     tile_n_bits, _ = tile_bits(tile_w, tile_h, C)
     offsets = torch.empty(C * T + 1, dtype=torch.int32, device=dev)
-    cursors = torch.empty(C * T, dtype=torch.int32, device=dev)
+    cursors = torch.empty(C * T * CSTRIDE, dtype=torch.int32, device=dev)
     n_dev = torch.empty(1, dtype=torch.int64, device=dev)
     overflow = torch.zeros(1, dtype=torch.int32, device=dev)
     call("gsb_tile_scan", ptr(tile_counts), C, tile_w, tile_h, ptr(offsets), ptr(cursors), ptr(n_dev),
@@ -263,7 +264,8 @@ def bin_tiles(means2d, radii, rec, tile_counts, tile_w, tile_h):
     if cap:
         call("gsb_isect_scatter", ptr(means2d), ptr(radii), ptr(rec), C, N, tile_w, tile_h, ptr(cursors),
              cap, ptr(depth_id), ptr(overflow), stream())
-        call("gsb_segment_sort", ptr(depth_id), ptr(offsets), C, tile_w, tile_h, tile_n_bits, cap,
+        call("gsb_segment_sort", ptr(depth_id), ptr(isect_ids), ptr(offsets), C, tile_w, tile_h,
+             tile_n_bits, cap,
              ptr(isect_ids), ptr(flatten_ids), stream())
     last_overflow, last_n_isects = overflow, n_dev
     return isect_ids, flatten_ids, offsets

@@ -31,6 +31,9 @@ extern "C" {
 #define GSB_CH 5              /* composited channels: r g b depth beta */
 #define GSB_TILE 16           /* tile edge in pixels (reference tile_size=16) */
 
+#define GSB_CSTRIDE 32         /* ints between per-tile counters: one 128-byte L2 line each,
+                                 because the L2 atomic unit serialises atomics per line */
+
 #define GSB_EINVAL (-1)       /* bad argument                         */
 #define GSB_EWORKSPACE (-2)   /* workspace too small                  */
 
@@ -46,7 +49,8 @@ int gsb_read_i64_host(const int64_t* src, int64_t* dst_host, void* stream);
  * Replaces gslam/rasterization.py:145-170, :187, :225-256 and the counting
  * half of isect_tiles (:261).  log_unc may be NULL (beta record slot = 0).
  * Outputs: radii[C,N] i32, means2d[C,N,2], rec[C,N,12], tiles_per_gauss[C,N] i32.
- * tile_counts[C, tile_h*tile_w] i32 (may be NULL; zeroed by the caller) receives the
+ * tile_counts[C*tile_h*tile_w*GSB_CSTRIDE] i32 (may be NULL; zeroed by the caller) receives
+ * at index i*GSB_CSTRIDE the
  * number of intersections per (camera, tile) for the tile-binned sort below. */
 int gsb_project_fwd(const float* means, const float* quats, const float* log_scales,
                     const float* logit_opacities, const float* logit_colors,
@@ -104,19 +108,22 @@ int gsb_sort_pairs(int64_t* keys_in, int32_t* vals_in, int64_t* keys_out, int32_
 /* K4+K5, tile-binned form (the product path; bit-identical to emit + stable sort +
  * offset encode, see csrc/binning.cu).  No step needs the intersection count I on
  * the host: it is offsets[C*T] (and *n_isects).
- *   gsb_tile_scan    : exclusive scan of tile_counts -> offsets[C*T+1] i32, cursors[C*T] i32
+ *   gsb_tile_scan    : exclusive scan of tile_counts -> offsets[C*T+1] i32 (dense) and
+ *                      cursors[C*T*GSB_CSTRIDE] i32 (strided like tile_counts)
  *   gsb_isect_scatter: (depth bits << 32 | flatten_id) into each tile's segment of
  *                      depth_id[capacity]; sets *overflow when I > capacity
- *   gsb_segment_sort : sorts every segment in shared memory and writes
- *                      isect_ids[capacity] i64, flatten_ids[capacity] i32 */
+ *   gsb_segment_sort : sorts every segment (bucket sort in shared memory; segments
+ *                      longer than 2048 keys go through scratch[capacity]) and writes
+ *                      isect_ids[capacity] i64, flatten_ids[capacity] i32; scratch may
+ *                      alias isect_ids */
 int gsb_tile_scan(const int32_t* tile_counts, int C, int tile_w, int tile_h, int32_t* offsets,
                   int32_t* cursors, int64_t* n_isects, void* stream);
 int gsb_isect_scatter(const float* means2d, const int32_t* radii, const float* rec, int C, int N,
                       int tile_w, int tile_h, int32_t* cursors, int64_t capacity,
                       int64_t* depth_id, int32_t* overflow, void* stream);
-int gsb_segment_sort(int64_t* depth_id, const int32_t* offsets, int C, int tile_w, int tile_h,
-                     int tile_n_bits, int64_t capacity, int64_t* isect_ids,
-                     int32_t* flatten_ids, void* stream);
+int gsb_segment_sort(int64_t* depth_id, int64_t* scratch, const int32_t* offsets, int C,
+                     int tile_w, int tile_h, int tile_n_bits, int64_t capacity,
+                     int64_t* isect_ids, int32_t* flatten_ids, void* stream);
 
 /* K5: isect_offset_encode (reference gslam/rasterization.py:274). */
 int gsb_isect_offsets(const int64_t* isect_ids, int64_t n_isects, int C, int tile_w,
