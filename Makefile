@@ -9,7 +9,7 @@ LIB := gslam_b200/libgsb.so
 
 all: $(LIB)
 
-build/%.o: $(SRC_DIR)/%.cu $(SRC_DIR)/common.cuh include/gsb.h
+build/%.o: $(SRC_DIR)/%.cu $(wildcard $(SRC_DIR)/*.cuh) include/gsb.h
 	@mkdir -p build
 	$(NVCC) $(NVFLAGS) -c $< -o $@ 2> build/$*.ptxas.log || (cat build/$*.ptxas.log; exit 1)
 
