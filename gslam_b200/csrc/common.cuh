@@ -44,6 +44,13 @@ __device__ __forceinline__ float fast_ex2(float x) {
     return y;
 }
 
+// 1/x on the SFU (MUFU.RCP), about 1 ulp.
+__device__ __forceinline__ float fast_rcp(float x) {
+    float y;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+
 __device__ __forceinline__ float sigmoidf_(float x) { return 1.0f / (1.0f + expf(-x)); }
 
 // Tile bounding box [x0,x1) x [y0,y1) of a splat, float32 arithmetic shared by

@@ -55,7 +55,9 @@ __device__ __forceinline__ float transpose_reduce16(const float (&v)[16], int la
     return d;
 }
 
-__global__ void __launch_bounds__(BWD_THREADS)
+// 9 CTAs per SM (<= 113 registers): 148 x 9 = 1332 slots hold all 1200 tiles of a 640x480 view in
+// one wave; at 8 per SM the last 16 tiles ran as a second wave on an otherwise idle GPU.
+__global__ void __launch_bounds__(BWD_THREADS, 9)
 composite_bwd_kernel(const float4* __restrict__ rec, const int32_t* __restrict__ flatten_ids,
                      const int32_t* __restrict__ offsets, const float* __restrict__ backgrounds, int C,
                      int width, int height, int tile_w, int tile_h, int64_t n_isects,
@@ -122,6 +124,9 @@ composite_bwd_kernel(const float4* __restrict__ rec, const int32_t* __restrict__
         }
     }
     const int warp_last = __reduce_max_sync(0xffffffffu, my_last);
+    int slot_last[PPT];
+#pragma unroll
+    for (int j = 0; j < PPT; ++j) slot_last[j] = __reduce_max_sync(0xffffffffu, bin_final[j]);
     if (lane == 0) s_max[warp] = warp_last;
     __syncthreads();
     const int block_last = max(s_max[0], s_max[1]);
@@ -135,12 +140,7 @@ composite_bwd_kernel(const float4* __restrict__ rec, const int32_t* __restrict__
         __syncthreads();
         for (int t = tid; t < bs; t += BWD_THREADS) {
             const int id = flatten_ids[b0 + t];
-            const float4* rp = rec + (size_t)id * 3;
-            float4 r0 = rp[0], r1 = rp[1];
-            r0.w *= 0.5f * LOG2E;
-            r1.x *= LOG2E;
-            r1.y *= 0.5f * LOG2E;
-            s0[t] = r0; s1[t] = r1; s2[t] = rp[2];
+            stage_splat(rec + (size_t)id * 3, s0[t], s1[t], s2[t]);
             s_id[t] = id;
         }
         {
@@ -150,47 +150,63 @@ composite_bwd_kernel(const float4* __restrict__ rec, const int32_t* __restrict__
         __syncthreads();
         for (int t = min(bs - 1, warp_last - b0); t >= 0; --t) {
             const int idx = b0 + t;
-            const float4 g0 = s0[t], g1 = s1[t];
+            const float4 g0 = s0[t];        // x, y, a', b'
+            const float4 g1 = s1[t];        // c', thr, opacity, r
+            // Phase 1, branch-free: sigma', exp and alpha of the four pixels (chains overlap)
+            const float dx0 = g0.x - pxf, dx1 = dx0 - 8.0f;
+            const float dy0 = g0.y - pyf, dy1 = dy0 - 4.0f;
+            const float ax0 = g0.z * dx0 * dx0, ax1 = g0.z * dx1 * dx1;
+            const float cy0 = g1.x * dy0 * dy0, cy1 = g1.x * dy1 * dy1;
+            const float bx0 = g0.w * dx0, bx1 = g0.w * dx1;
+            float sigma[PPT], vis[PPT], alpha[PPT];
+            sigma[0] = fmaf(bx0, dy0, ax0 + cy0);
+            sigma[1] = fmaf(bx1, dy0, ax1 + cy0);
+            sigma[2] = fmaf(bx0, dy1, ax0 + cy1);
+            sigma[3] = fmaf(bx1, dy1, ax1 + cy1);
+            bool valid[PPT];
+            unsigned votes[PPT];
+#pragma unroll
+            for (int j = 0; j < PPT; ++j) {
+                vis[j] = fast_ex2(-sigma[j]);
+                alpha[j] = fminf(ALPHA_MAX, g1.z * vis[j]);
+                valid[j] = idx <= bin_final[j] && sigma[j] >= 0.f && alpha[j] >= ALPHA_MIN;
+            }
+#pragma unroll
+            for (int j = 0; j < PPT; ++j) votes[j] = __ballot_sync(0xffffffffu, valid[j]);
+            if ((votes[0] | votes[1] | votes[2] | votes[3]) == 0u) continue;
+            const float4 g2 = s2[t];        // g, b, depth, beta
+            const float col[GSB_CH] = {g1.w, g2.x, g2.y, g2.z, g2.w};
             float g[16];
 #pragma unroll
             for (int k = 0; k < 16; ++k) g[k] = 0.f;
-            bool any_hit = false;
+            // Phase 2: per 8x4 block, a warp-uniform branch; inside, misses are predicated (alpha = 0)
 #pragma unroll
             for (int j = 0; j < PPT; ++j) {
-                const float dx = g0.x - (pxf + (float)((j & 1) * 8));
-                const float dy = g0.y - (pyf + (float)((j >> 1) * 4));
-                const float sigma = g0.w * dx * dx + g1.y * dy * dy + g1.x * dx * dy;   // * log2(e)
-                const float vis = fast_ex2(-sigma);
-                const float alpha = fminf(ALPHA_MAX, g0.z * vis);
-                const bool valid = idx <= bin_final[j] && sigma >= 0.f && alpha >= ALPHA_MIN;
-                if (!__any_sync(0xffffffffu, valid)) continue;
-                any_hit = true;
-                if (valid) {
-                    const float4 g2 = s2[t];
-                    const float col[GSB_CH] = {g1.z, g1.w, g2.x, g2.y, g2.z};
-                    const float ra = 1.0f / (1.0f - alpha);
-                    T[j] *= ra;
-                    const float fac = alpha * T[j];
-                    float v_alpha = tail[j] * ra;
+                if (votes[j] == 0u) continue;
+                const float dx = (j & 1) ? dx1 : dx0, dy = (j >> 1) ? dy1 : dy0;
+                const float al = valid[j] ? alpha[j] : 0.f;
+                const float ra = fast_rcp(1.0f - al);
+                const float Tn = T[j] * ra;
+                const float fac = al * Tn;
+                float v_alpha = tail[j] * ra;
 #pragma unroll
-                    for (int k = 0; k < GSB_CH; ++k) {
-                        g[6 + k] += fac * vr[j][k];
-                        v_alpha += (col[k] * T[j] - buf[j][k] * ra) * vr[j][k];
-                        buf[j][k] += col[k] * fac;
-                    }
-                    if (g0.z * vis <= ALPHA_MAX) {
-                        const float v_sigma = -g0.z * vis * v_alpha;
-                        const float vsp = v_sigma * (1.0f / LOG2E);
-                        g[0] += vsp * (2.f * g0.w * dx + g1.x * dy);
-                        g[1] += vsp * (g1.x * dx + 2.f * g1.y * dy);
-                        g[2] += vis * v_alpha;
-                        g[3] += 0.5f * v_sigma * dx * dx;
-                        g[4] += v_sigma * dx * dy;
-                        g[5] += 0.5f * v_sigma * dy * dy;
-                    }
+                for (int k = 0; k < GSB_CH; ++k) {
+                    g[6 + k] = fmaf(fac, vr[j][k], g[6 + k]);
+                    v_alpha = fmaf(fmaf(col[k], Tn, -buf[j][k] * ra), vr[j][k], v_alpha);
+                    buf[j][k] = fmaf(col[k], fac, buf[j][k]);
                 }
+                T[j] = Tn;
+                const float ov = g1.z * vis[j];
+                const float v_sigma = (valid[j] && ov <= ALPHA_MAX) ? -ov * v_alpha : 0.f;
+                const float v_op = (valid[j] && ov <= ALPHA_MAX) ? vis[j] * v_alpha : 0.f;
+                const float vsp = v_sigma * (1.0f / LOG2E);
+                g[0] = fmaf(vsp, 2.f * g0.z * dx + g0.w * dy, g[0]);
+                g[1] = fmaf(vsp, g0.w * dx + 2.f * g1.x * dy, g[1]);
+                g[2] += v_op;
+                g[3] = fmaf(0.5f * v_sigma * dx, dx, g[3]);
+                g[4] = fmaf(v_sigma * dx, dy, g[4]);
+                g[5] = fmaf(0.5f * v_sigma * dy, dy, g[5]);
             }
-            if (!any_hit) continue;
             int slot;
             const float total = transpose_reduce16(g, lane, slot);
             if (!(lane & 1) && slot < 11 && total != 0.f) atomicAdd(&s_acc[t][slot], total);
