@@ -1,0 +1,281 @@
+// K9/K10: fused SSIM and photometric loss.
+//
+// K9 replaces fused_ssim (rahul-goel/fused-ssim@30fb258) as called at reference
+// gslam/backend.py:303-307: 11-tap sigma=1.5 separable Gaussian window with zero
+// padding, C1 = 0.01^2, C2 = 0.03^2, per channel; padding='valid' averages the
+// map without its 5-pixel border.  Images are addressed through element strides
+// so the reference's `rgbs.permute(0, 3, 1, 2)` view needs no copy.
+//
+// K10 replaces the exposure-affine + active-NeRF terms (gslam/backend.py:273-283,
+// gslam/frontend.py:121-129): because every term is a mean over pixels the
+// gradient is local, so ONE pass produces the loss sums and the gradients.
+#include "common.cuh"
+
+__constant__ float G11[11] = {1.0283800845e-03f, 7.5987581352e-03f, 3.6000772128e-02f, 1.0936068951e-01f,
+                              2.1300553771e-01f, 2.6601172486e-01f, 2.1300553771e-01f, 1.0936068951e-01f,
+                              3.6000772128e-02f, 7.5987581352e-03f, 1.0283800845e-03f};
+#define SSIM_C1 (0.01f * 0.01f)
+#define SSIM_C2 (0.03f * 0.03f)
+#define SB 16
+#define SH (SB + 10)
+
+struct Strides4 {
+    int64_t n, c, h, w;
+};
+
+__device__ __forceinline__ float block_sum_256(float v, float* red) {
+    v = warp_sum(v);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+    __syncthreads();
+    float s = 0.f;
+    if (threadIdx.x < 8) s = red[threadIdx.x];
+    if (threadIdx.x < 32) {
+        s += __shfl_xor_sync(0xffffffffu, s, 4);
+        s += __shfl_xor_sync(0xffffffffu, s, 2);
+        s += __shfl_xor_sync(0xffffffffu, s, 1);
+    }
+    return s;   // valid in thread 0
+}
+
+// grid (ceil(W/16), ceil(H/16), N*C), block 256 (tx = tid & 15, ty = tid >> 4)
+__global__ void __launch_bounds__(256)
+ssim_fwd_kernel(const float* __restrict__ img1, const float* __restrict__ img2, Strides4 s1, Strides4 s2,
+                int C, int H, int W, int valid, float* __restrict__ ssim_sum,
+                float* __restrict__ dm_dmu1, float* __restrict__ dm_ds1, float* __restrict__ dm_ds12) {
+    __shared__ float sx[SH][SH + 1], sy[SH][SH + 1];
+    __shared__ float hc[5][SH][SB];
+    __shared__ float red[8];
+    const int nc = blockIdx.z, n = nc / C, c = nc % C;
+    const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+    const int h0 = blockIdx.y * SB, w0 = blockIdx.x * SB;
+    const float* p1 = img1 + n * s1.n + c * s1.c;
+    const float* p2 = img2 + n * s2.n + c * s2.c;
+    for (int i = tid; i < SH * SH; i += 256) {
+        int r = i / SH, q = i % SH;
+        int gh = h0 + r - 5, gw = w0 + q - 5;
+        bool in = gh >= 0 && gh < H && gw >= 0 && gw < W;
+        sx[r][q] = in ? p1[gh * s1.h + gw * s1.w] : 0.f;
+        sy[r][q] = in ? p2[gh * s2.h + gw * s2.w] : 0.f;
+    }
+    __syncthreads();
+    for (int i = tid; i < SH * SB; i += 256) {
+        int r = i / SB, q = i % SB;
+        float m1 = 0.f, m2 = 0.f, xx = 0.f, yy = 0.f, xy = 0.f;
+#pragma unroll
+        for (int k = 0; k < 11; ++k) {
+            float x = sx[r][q + k], y = sy[r][q + k], w = G11[k];
+            m1 += w * x; m2 += w * y; xx += w * x * x; yy += w * y * y; xy += w * x * y;
+        }
+        hc[0][r][q] = m1; hc[1][r][q] = m2; hc[2][r][q] = xx; hc[3][r][q] = yy; hc[4][r][q] = xy;
+    }
+    __syncthreads();
+    float mu1 = 0.f, mu2 = 0.f, e11 = 0.f, e22 = 0.f, e12 = 0.f;
+#pragma unroll
+    for (int k = 0; k < 11; ++k) {
+        float w = G11[k];
+        mu1 += w * hc[0][ty + k][tx]; mu2 += w * hc[1][ty + k][tx]; e11 += w * hc[2][ty + k][tx];
+        e22 += w * hc[3][ty + k][tx]; e12 += w * hc[4][ty + k][tx];
+    }
+    const int h = h0 + ty, w = w0 + tx;
+    const bool inside = h < H && w < W;
+    const bool counted = inside && (!valid || (h >= 5 && h < H - 5 && w >= 5 && w < W - 5));
+    const float sg1 = e11 - mu1 * mu1, sg2 = e22 - mu2 * mu2, sg12 = e12 - mu1 * mu2;
+    const float A1 = 2.f * mu1 * mu2 + SSIM_C1, A2 = 2.f * sg12 + SSIM_C2;
+    const float B1 = mu1 * mu1 + mu2 * mu2 + SSIM_C1, B2 = sg1 + sg2 + SSIM_C2;
+    const float inv = 1.0f / (B1 * B2);
+    const float m = A1 * A2 * inv;
+    if (dm_dmu1 && inside) {
+        // m as a function of (mu1, E[x^2], E[xy]) with img2 fixed
+        float d_mu1 = 0.f, d_s1 = 0.f, d_s12 = 0.f;
+        if (counted) {
+            d_mu1 = (2.f * mu2 * (A2 - A1) * inv) - m * 2.f * mu1 * (B2 - B1) * inv;
+            d_s1 = -m / B2;
+            d_s12 = 2.f * A1 * inv;
+        }
+        size_t o = ((size_t)nc * H + h) * W + w;
+        dm_dmu1[o] = d_mu1; dm_ds1[o] = d_s1; dm_ds12[o] = d_s12;
+    }
+    float tot = block_sum_256(counted ? m : 0.f, red);
+    if (tid == 0 && tot != 0.f) atomicAdd(ssim_sum, tot);
+}
+
+// v_img1[p] (+)= scale * sum_q w(q-p) [ dmu1(q) + 2 x(p) ds1(q) + y(p) ds12(q) ],  scale = *grad * coef
+__global__ void __launch_bounds__(256)
+ssim_bwd_kernel(const float* __restrict__ img1, const float* __restrict__ img2, Strides4 s1, Strides4 s2,
+                int C, int H, int W, const float* __restrict__ dm_dmu1, const float* __restrict__ dm_ds1,
+                const float* __restrict__ dm_ds12, const float* __restrict__ grad, float coef,
+                float* __restrict__ v_img1, Strides4 so, int accumulate) {
+    __shared__ float sa[3][SH][SH + 1];
+    __shared__ float hc[3][SH][SB];
+    const int nc = blockIdx.z, n = nc / C, c = nc % C;
+    const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+    const int h0 = blockIdx.y * SB, w0 = blockIdx.x * SB;
+    const size_t plane = (size_t)nc * H * W;
+    for (int i = tid; i < SH * SH; i += 256) {
+        int r = i / SH, q = i % SH;
+        int gh = h0 + r - 5, gw = w0 + q - 5;
+        bool in = gh >= 0 && gh < H && gw >= 0 && gw < W;
+        size_t o = plane + (size_t)gh * W + gw;
+        sa[0][r][q] = in ? dm_dmu1[o] : 0.f;
+        sa[1][r][q] = in ? dm_ds1[o] : 0.f;
+        sa[2][r][q] = in ? dm_ds12[o] : 0.f;
+    }
+    __syncthreads();
+    for (int i = tid; i < SH * SB; i += 256) {
+        int r = i / SB, q = i % SB;
+        float a = 0.f, b = 0.f, d = 0.f;
+#pragma unroll
+        for (int k = 0; k < 11; ++k) {
+            float w = G11[k];
+            a += w * sa[0][r][q + k]; b += w * sa[1][r][q + k]; d += w * sa[2][r][q + k];
+        }
+        hc[0][r][q] = a; hc[1][r][q] = b; hc[2][r][q] = d;
+    }
+    __syncthreads();
+    float a = 0.f, b = 0.f, d = 0.f;
+#pragma unroll
+    for (int k = 0; k < 11; ++k) {
+        float w = G11[k];
+        a += w * hc[0][ty + k][tx]; b += w * hc[1][ty + k][tx]; d += w * hc[2][ty + k][tx];
+    }
+    const int h = h0 + ty, w = w0 + tx;
+    if (h >= H || w >= W) return;
+    const float x = img1[n * s1.n + c * s1.c + h * s1.h + w * s1.w];
+    const float y = img2[n * s2.n + c * s2.c + h * s2.h + w * s2.w];
+    const float g = (grad ? *grad : 1.0f) * coef * (a + 2.f * x * b + y * d);
+    float* dst = v_img1 + n * so.n + c * so.c + h * so.h + w * so.w;
+    *dst = accumulate ? *dst + g : g;
+}
+
+static Strides4 mk(const int64_t* s) { return Strides4{s[0], s[1], s[2], s[3]}; }
+
+GSB_API int gsb_ssim_fwd(const float* img1, const float* img2, const int64_t* strides1_host,
+                         const int64_t* strides2_host, int N, int C, int H, int W, int valid,
+                         float* ssim_sum, float* dm_dmu1, float* dm_ds1, float* dm_ds12, void* stream) {
+    GSB_CHECK_ARG(N >= 0 && C >= 0 && H > 0 && W > 0);
+    if (N * C == 0) return 0;
+    GSB_CHECK_ARG(img1 && img2 && strides1_host && strides2_host && ssim_sum && N * C <= 65535);
+    GSB_CHECK_ARG((dm_dmu1 == nullptr) == (dm_ds1 == nullptr) && (dm_ds1 == nullptr) == (dm_ds12 == nullptr));
+    dim3 grid((W + SB - 1) / SB, (H + SB - 1) / SB, N * C);
+    ssim_fwd_kernel<<<grid, 256, 0, gsb_stream(stream)>>>(img1, img2, mk(strides1_host), mk(strides2_host), C, H, W,
+                                                          valid, ssim_sum, dm_dmu1, dm_ds1, dm_ds12);
+    GSB_LAUNCH_CHECK();
+    return 0;
+}
+
+GSB_API int gsb_ssim_bwd(const float* img1, const float* img2, const int64_t* strides1_host,
+                         const int64_t* strides2_host, int N, int C, int H, int W, const float* dm_dmu1,
+                         const float* dm_ds1, const float* dm_ds12, const float* grad, float coef,
+                         float* v_img1, const int64_t* strides_out_host, int accumulate, void* stream) {
+    GSB_CHECK_ARG(N >= 0 && C >= 0 && H > 0 && W > 0);
+    if (N * C == 0) return 0;
+    GSB_CHECK_ARG(img1 && img2 && strides1_host && strides2_host && dm_dmu1 && dm_ds1 && dm_ds12 && v_img1 &&
+                  strides_out_host && N * C <= 65535);
+    dim3 grid((W + SB - 1) / SB, (H + SB - 1) / SB, N * C);
+    ssim_bwd_kernel<<<grid, 256, 0, gsb_stream(stream)>>>(img1, img2, mk(strides1_host), mk(strides2_host), C, H, W,
+                                                          dm_dmu1, dm_ds1, dm_ds12, grad, coef, v_img1,
+                                                          mk(strides_out_host), accumulate);
+    GSB_LAUNCH_CHECK();
+    return 0;
+}
+
+// ---------------------------------------------------------------------------
+// K10: photometric loss, value and gradient in one pass.
+//   mode 0  mapping active-NeRF NLL   mean(sum_ch e^2 / (2 beta^2)) + mean(0.5 ln^2 beta)
+//   mode 1  tracking 'active-nerf'    mean(sum_ch e^2 beta^-2)
+//   mode 2  'l1'                      mean over pixels and channels of |e|
+//   mode 3  'mse'                     mean over pixels and channels of e^2
+// e = rgb * exp(a_c) + b_c - gt (exposure[C,2] = (a, b); NULL = identity).
+// grid (ceil(H*W/256), C)
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+photo_loss_kernel(const float* __restrict__ render, const float* __restrict__ gt,
+                  const float* __restrict__ exposure, int mode, int HW, float inv_count, float coef,
+                  float* __restrict__ loss_sum, float* __restrict__ v_render,
+                  float* __restrict__ v_exposure) {
+    __shared__ float red[8];
+    const int cam = blockIdx.y;
+    const int p = blockIdx.x * 256 + threadIdx.x;
+    float ea = 1.f, eb = 0.f;
+    if (exposure) { ea = expf(exposure[cam * 2]); eb = exposure[cam * 2 + 1]; }
+    float t1 = 0.f, t2 = 0.f, ga = 0.f, gb = 0.f;
+    if (p < HW) {
+        const size_t pix = (size_t)cam * HW + p;
+        const float* r = render + pix * GSB_CH;
+        const float* g = gt + pix * 3;
+        const float beta = r[4];
+        float e[3], vr[3], vbeta = 0.f, se = 0.f;
+#pragma unroll
+        for (int k = 0; k < 3; ++k) { e[k] = r[k] * ea + eb - g[k]; se += e[k] * e[k]; }
+        if (mode == 0) {
+            const float ib2 = 1.0f / (beta * beta), lb = logf(beta);
+            t1 = 0.5f * se * ib2; t2 = 0.5f * lb * lb;
+#pragma unroll
+            for (int k = 0; k < 3; ++k) vr[k] = e[k] * ib2;
+            vbeta = (-se * ib2 + lb) / beta;
+        } else if (mode == 1) {
+            const float ib2 = 1.0f / (beta * beta);
+            t1 = se * ib2;
+#pragma unroll
+            for (int k = 0; k < 3; ++k) vr[k] = 2.f * e[k] * ib2;
+            vbeta = -2.f * se * ib2 / beta;
+        } else if (mode == 2) {
+            t1 = (fabsf(e[0]) + fabsf(e[1]) + fabsf(e[2])) * (1.f / 3.f);
+#pragma unroll
+            for (int k = 0; k < 3; ++k) vr[k] = (e[k] > 0.f ? 1.f : (e[k] < 0.f ? -1.f : 0.f)) * (1.f / 3.f);
+        } else {
+            t1 = se * (1.f / 3.f);
+#pragma unroll
+            for (int k = 0; k < 3; ++k) vr[k] = 2.f * e[k] * (1.f / 3.f);
+        }
+        const float sc = inv_count * coef;
+        float* o = v_render + pix * GSB_CH;
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            o[k] = sc * vr[k] * ea;
+            ga += sc * vr[k] * r[k] * ea;
+            gb += sc * vr[k];
+        }
+        o[3] = 0.f;
+        o[4] = sc * vbeta;
+    }
+    float s;
+    s = block_sum_256(t1, red); if (threadIdx.x == 0 && s != 0.f) atomicAdd(loss_sum, s);
+    __syncthreads();
+    s = block_sum_256(t2, red); if (threadIdx.x == 0 && s != 0.f) atomicAdd(loss_sum + 1, s);
+    if (v_exposure) {
+        __syncthreads();
+        s = block_sum_256(ga, red); if (threadIdx.x == 0 && s != 0.f) atomicAdd(v_exposure + cam * 2, s);
+        __syncthreads();
+        s = block_sum_256(gb, red); if (threadIdx.x == 0 && s != 0.f) atomicAdd(v_exposure + cam * 2 + 1, s);
+    }
+}
+
+GSB_API int gsb_photo_loss(const float* render, const float* gt, const float* exposure, int mode, int C,
+                           int H, int W, float coef, float* loss_sum, float* v_render,
+                           float* v_exposure, void* stream) {
+    GSB_CHECK_ARG(C >= 0 && H > 0 && W > 0 && mode >= 0 && mode <= 3);
+    if (C == 0) return 0;
+    GSB_CHECK_ARG(render && gt && loss_sum && v_render && C <= 65535);
+    const int HW = H * W;
+    dim3 grid((HW + 255) / 256, C);
+    photo_loss_kernel<<<grid, 256, 0, gsb_stream(stream)>>>(render, gt, exposure, mode, HW,
+                                                            1.0f / ((float)C * (float)HW), coef, loss_sum,
+                                                            v_render, v_exposure);
+    GSB_LAUNCH_CHECK();
+    return 0;
+}
+
+// v_render[C,H,W,5] *= *grad  (device scalar), used when the fused loss is not the graph root
+__global__ void scale_kernel(float* __restrict__ x, int64_t n, const float* __restrict__ grad) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) x[i] *= *grad;
+}
+
+GSB_API int gsb_scale_by_scalar(float* x, int64_t n, const float* grad, void* stream) {
+    if (n == 0) return 0;
+    GSB_CHECK_ARG(x && grad);
+    scale_kernel<<<(unsigned)((n + 255) / 256), 256, 0, gsb_stream(stream)>>>(x, n, grad);
+    GSB_LAUNCH_CHECK();
+    return 0;
+}

@@ -1,0 +1,63 @@
+"""Single-launch Adam for the splat parameters (K12/K13).
+
+`FusedAdam` is a `torch.optim.Optimizer` whose per-parameter state has the keys
+torch's Adam uses (`step`, `exp_avg`, `exp_avg_sq`, leading dimension N), so the
+reference's optimizer-state surgery on insertion / pruning (gslam/insertion.py:51-62,
+gslam/pruning.py:36-45) works on it unchanged.  `step()` updates every parameter of
+every group with ONE kernel launch (the reference steps seven optimizers,
+gslam/backend.py:559-563) and can fold in the opacity decay of gslam/backend.py:356-359.
+"""
+from __future__ import annotations
+
+import ctypes as ct
+from typing import Optional
+
+import torch
+
+from ._lib import AdamTensor, call, stream
+
+
+class FusedAdam(torch.optim.Optimizer):
+    def __init__(self, params, lr: float = 1e-3, betas=(0.9, 0.999), eps: float = 1e-8):
+        super().__init__(params, dict(lr=lr, betas=betas, eps=eps))
+
+    def _state(self, p):
+        st = self.state[p]
+        if len(st) == 0:
+            st["step"] = torch.tensor(0.0)
+            st["exp_avg"] = torch.zeros_like(p, memory_format=torch.preserve_format)
+            st["exp_avg_sq"] = torch.zeros_like(p, memory_format=torch.preserve_format)
+        return st
+
+    @torch.no_grad()
+    def step(self, closure=None, decay_param: Optional[torch.Tensor] = None,
+             vis_count: Optional[torch.Tensor] = None, decay: float = 0.995):
+        """decay_param (e.g. the opacity logits) is multiplied by `decay` where
+        vis_count (int32, one entry per row of decay_param) > 1."""
+        loss = closure() if closure is not None else None
+        buckets = {}   # (step, betas, eps) -> list of (p, grad, state, lr)
+        for group in self.param_groups:
+            for p in group["params"]:
+                if p.grad is None:
+                    continue
+                if not (p.is_cuda and p.dtype == torch.float32 and p.is_contiguous()):
+                    raise RuntimeError("FusedAdam needs contiguous float32 CUDA parameters")
+                st = self._state(p)
+                st["step"] += 1
+                key = (int(st["step"]), tuple(group["betas"]), group["eps"])
+                buckets.setdefault(key, []).append((p, p.grad.contiguous(), st, group["lr"]))
+        for (step, betas, eps), items in buckets.items():
+            for i in range(0, len(items), 8):
+                chunk = items[i:i + 8]
+                arr = (AdamTensor * len(chunk))()
+                decay_idx, vis_div = -1, 1
+                for k, (p, g, st, lr) in enumerate(chunk):
+                    arr[k] = AdamTensor(p.data_ptr(), g.data_ptr(), st["exp_avg"].data_ptr(),
+                                        st["exp_avg_sq"].data_ptr(), p.numel(), lr)
+                    if decay_param is not None and p is decay_param:
+                        decay_idx = k
+                        vis_div = max(p.numel() // max(vis_count.numel(), 1), 1)
+                vc = vis_count.data_ptr() if decay_idx >= 0 else None
+                call("gsb_adam_multi", ct.cast(arr, ct.c_void_p), len(chunk), betas[0], betas[1], eps, step,
+                     decay_idx, vc, vis_div, decay, stream())
+        return loss

@@ -160,6 +160,7 @@ def rasterization(
         opacities=rec[..., 2],
         n_touched=n_touched.long(),
     )
+    out.render = render   # [C,H,W,5] (r g b depth beta); input of losses.photometric_ssim_loss
     return out
 
 

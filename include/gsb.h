@@ -151,6 +151,51 @@ int gsb_composite_bwd(const float* rec, const int32_t* flatten_ids, const int32_
                       const int32_t* last_ids, const float* v_render, const float* v_alphas,
                       float* v_rec, float* v_backgrounds, void* stream);
 
+/* K9: fused_ssim (reference gslam/backend.py:303-307; rahul-goel/fused-ssim@30fb258).
+ * img1/img2 are [N,C,H,W] addressed through element strides (host arrays of 4: n, c, h, w),
+ * so channels-last views need no copy.  valid != 0 is padding='valid' (the 5-pixel border is
+ * left out of the mean).  ssim_sum (zeroed by the caller) receives the SUM of the SSIM map over
+ * the counted pixels.  dm_* [N,C,H,W] (all three or none) receive the partial derivatives the
+ * backward pass needs.  gsb_ssim_bwd writes (accumulate == 0) or adds (!= 0)
+ *   (*grad) * coef * d(ssim_sum)/d(img1)   into v_img1 (element strides strides_out_host);
+ * grad is a DEVICE scalar (NULL = 1) so the upstream gradient needs no host sync. */
+int gsb_ssim_fwd(const float* img1, const float* img2, const int64_t* strides1_host,
+                 const int64_t* strides2_host, int N, int C, int H, int W, int valid,
+                 float* ssim_sum, float* dm_dmu1, float* dm_ds1, float* dm_ds12, void* stream);
+int gsb_ssim_bwd(const float* img1, const float* img2, const int64_t* strides1_host,
+                 const int64_t* strides2_host, int N, int C, int H, int W, const float* dm_dmu1,
+                 const float* dm_ds1, const float* dm_ds12, const float* grad, float coef,
+                 float* v_img1, const int64_t* strides_out_host, int accumulate, void* stream);
+
+/* K10: photometric loss, value AND gradient in one pass (reference gslam/backend.py:273-283,
+ * gslam/frontend.py:121-129).  render[C,H,W,5] (r g b depth beta), gt[C,H,W,3],
+ * exposure[C,2] = (a, b) or NULL; e = rgb * exp(a) + b - gt.
+ *   mode 0: mean(sum_ch e^2 / (2 beta^2)) + mean(0.5 ln^2 beta)      (mapping, active-NeRF)
+ *   mode 1: mean(sum_ch e^2 beta^-2)   mode 2: mean |e|   mode 3: mean e^2   (tracking)
+ * loss_sum[2] (zeroed by the caller) receives the two un-normalised sums; v_render[C,H,W,5]
+ * is overwritten with coef * dLoss/drender; v_exposure[C,2] (zeroed; may be NULL) accumulates
+ * coef * dLoss/dexposure. */
+int gsb_photo_loss(const float* render, const float* gt, const float* exposure, int mode, int C,
+                   int H, int W, float coef, float* loss_sum, float* v_render,
+                   float* v_exposure, void* stream);
+int gsb_scale_by_scalar(float* x, int64_t n, const float* grad, void* stream);
+
+/* K12/K13: ONE launch of Adam over up to 8 tensors (reference gslam/backend.py:559-602 steps
+ * seven optimizers) with torch.optim.Adam default semantics; `step` is the 1-based count of this
+ * update.  Tensor `decay_tensor` (-1: none) additionally gets the opacity decay of
+ * gslam/backend.py:356-359: element i is multiplied by `decay` when vis_count[i / vis_div] > 1. */
+typedef struct {
+    float* param;
+    const float* grad;
+    float* exp_avg;
+    float* exp_avg_sq;
+    int64_t n;
+    float lr;
+} gsb_adam_tensor;
+int gsb_adam_multi(const gsb_adam_tensor* tensors_host, int n_tensors, float beta1, float beta2,
+                   float eps, int step, int decay_tensor, const int32_t* vis_count, int vis_div,
+                   float decay, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
