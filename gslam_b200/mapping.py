@@ -1,0 +1,149 @@
+"""View-sharded mapping step: the body of Backend.optimize_map (reference
+gslam/backend.py:260-359) with the keyframe window split across ranks.
+
+The reference is single-GPU.  Each view's projection / binning / compositing /
+image loss is independent given the (replicated) Gaussians, so rank r of p
+renders views window[r::p] and ONE all-reduce of the flat [15 N] gradient buffer
+(means | quats | scales | opacities | colors | log_uncertainties) per step makes
+every rank apply the identical Adam update; parameters never need a broadcast
+after step 0.  Pose / exposure gradients stay on the rank that owns the view.
+
+Host-side pieces (sharding, loss scaling, flat-gradient reduction, the analytic
+isotropic-regulariser gradient) are plain functions so they can be tested on the
+CPU with the gloo backend; the renderer is `gslam_b200.rasterization`.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import Callable, List, Optional, Sequence
+
+import torch
+import torch.distributed as dist
+from torch import Tensor
+
+PARAM_NAMES = ("means", "quats", "scales", "opacities", "colors", "log_uncertainties")
+PARAM_WIDTH = (3, 4, 3, 1, 3, 1)          # 15 floats per Gaussian
+# learning rates of reference MapConfig (gslam/backend.py:53-58)
+DEFAULT_LRS = dict(means=1.6e-3, quats=5e-3, scales=5e-3, opacities=2.5e-2, colors=1e-2,
+                   log_uncertainties=2.5e-3)
+
+
+def shard_views(n_views: int, rank: int, world: int) -> List[int]:
+    """Views of the window rendered by `rank`: window[rank::world]."""
+    return list(range(rank, n_views, world))
+
+
+class FlatSplats:
+    """The six per-splat tensors as views of ONE flat [15 N] buffer (same for the gradients)."""
+
+    def __init__(self, tensors: Sequence[Tensor]):
+        n = tensors[0].shape[0]
+        dev, dt = tensors[0].device, tensors[0].dtype
+        self.n = n
+        self.flat = torch.empty(15 * n, device=dev, dtype=dt)
+        self.params: List[Tensor] = []
+        o = 0
+        for t, w in zip(tensors, PARAM_WIDTH):
+            v = self.flat[o:o + w * n].view((n, w) if w > 1 else (n,))
+            v.copy_(t.detach().reshape(v.shape))
+            self.params.append(v.requires_grad_(True))
+            o += w * n
+
+    def flat_grad(self) -> Tensor:
+        """The [15 N] gradient; zero-copy when the grads are still views of project_bwd's buffer."""
+        grads = [p.grad for p in self.params]
+        base = grads[0]._base if grads[0] is not None else None
+        if base is not None and base.numel() == 15 * self.n and all(
+                g is not None and g._base is base for g in grads):
+            return base
+        flat = torch.cat([(g if g is not None else torch.zeros_like(p)).reshape(-1)
+                          for g, p in zip(grads, self.params)])
+        o = 0
+        for p, w in zip(self.params, PARAM_WIDTH):
+            p.grad = flat[o:o + w * self.n].view(p.shape)
+            o += w * self.n
+        return flat
+
+
+@torch.no_grad()
+def add_isotropic_grad_(scales_grad: Tensor, log_scales: Tensor, visible: Tensor, weight: float):
+    """d/d log_scales of  weight * sum_visible |exp(s) - exp(mean_axis s).detach()|
+    (gslam/backend.py:286-296), added in place; returns the loss value."""
+    s = log_scales.detach()
+    e = s.exp()
+    m = s.mean(dim=1, keepdim=True).exp()
+    vis = visible[:, None].to(s.dtype)
+    scales_grad.add_(weight * torch.sign(e - m) * e * vis)
+    return ((e - m).abs() * vis).sum()
+
+
+def edge_aware_tv(depth: Tensor, rgb: Tensor, mask: Tensor) -> Tensor:
+    """Edge-aware total variation of the depth map (reference gslam/utils.py:136-161):
+    |d depth| * exp(-mean_ch |d rgb|) summed over the masked horizontal and vertical neighbours."""
+    ddx = (depth[..., :, :-1] - depth[..., :, 1:]).abs()
+    ddy = (depth[..., :-1, :] - depth[..., 1:, :]).abs()
+    wx = torch.exp(-(rgb[..., :, :-1, :] - rgb[..., :, 1:, :]).abs().mean(-1))
+    wy = torch.exp(-(rgb[..., :-1, :, :] - rgb[..., 1:, :, :]).abs().mean(-1))
+    return (ddx * wx * mask[..., :, :-1]).sum() + (ddy * wy * mask[..., :-1, :]).sum()
+
+
+def allreduce_sum_(t: Tensor, group=None) -> Tensor:
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.SUM, group=group)
+    return t
+
+
+@dataclass
+class MappingStepResult:
+    total: Tensor
+    photometric: Tensor
+    radii: Tensor
+    n_touched: Tensor
+    vis_count: Tensor
+
+
+class MappingStep:
+    """fwd + losses + bwd + gradient all-reduce + Adam + opacity decay for this rank's views."""
+
+    def __init__(self, splats: FlatSplats, optimizer, render_fn: Optional[Callable] = None,
+                 loss_fn: Optional[Callable] = None, ssim_weight: float = 0.2,
+                 isotropic_weight: float = 5e-4, opacity_decay: float = 0.995, depth_tv_weight: float = 0.0,
+                 group=None):
+        if render_fn is None:
+            from .rasterization import rasterization as render_fn
+        if loss_fn is None:
+            from .losses import photometric_ssim_loss as loss_fn
+        self.splats, self.opt = splats, optimizer
+        self.render_fn, self.loss_fn = render_fn, loss_fn
+        self.ssim_weight, self.iso_w, self.decay, self.group = ssim_weight, isotropic_weight, opacity_decay, group
+        self.tv_w = depth_tv_weight
+
+    def __call__(self, viewmats: Tensor, Ks: Tensor, gt_imgs: Tensor, exposure: Optional[Tensor],
+                 width: int, height: int, n_views_total: int, background: Optional[Tensor] = None,
+                 step_optimizer: bool = True) -> MappingStepResult:
+        P = self.splats.params
+        for p in P:
+            p.grad = None
+        c_local = viewmats.shape[0]
+        bg = background if background is not None else torch.zeros(c_local, 3, device=viewmats.device)
+        out = self.render_fn(P[0], P[1], P[2], P[3], P[4], viewmats, Ks, width, height, packed=False,
+                             render_mode="RGB+D", log_uncertainties=P[5], backgrounds=bg)
+        # the image losses are means over ALL views of the window: weight this rank's share
+        total, photo = self.loss_fn(out.render, gt_imgs, exposure, self.ssim_weight, "mapping")
+        share = c_local / float(n_views_total)
+        loss = total * share
+        if self.tv_w:
+            # a sum (not a mean) over this rank's views: no share factor (gslam/backend.py:297-318)
+            loss = loss + self.tv_w * edge_aware_tv(out.depthmaps, out.rgbs, out.alphas[..., 0] > 0.4)
+        loss.backward()
+        vis_count = (out.radii > 0).sum(dim=0).to(torch.int32)
+        allreduce_sum_(vis_count, self.group)
+        flat = self.splats.flat_grad()
+        allreduce_sum_(flat, self.group)                      # the one gradient collective of the step
+        # isotropic regulariser on the union visibility, identical on every rank, after the reduce
+        iso = add_isotropic_grad_(P[2].grad, P[2], vis_count > 0, self.iso_w)
+        if step_optimizer:
+            self.opt.step(decay_param=P[3], vis_count=vis_count, decay=self.decay)
+        stats = torch.stack([total.detach() * share, photo.detach() * share])
+        allreduce_sum_(stats, self.group)
+        return MappingStepResult(stats[0] + self.iso_w * iso, stats[1], out.radii, out.n_touched, vis_count)
