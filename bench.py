@@ -187,11 +187,11 @@ def run_ours(args):
     bg = torch.zeros(1, 3, device=dev)
     flush_buf = torch.empty(256 << 20, dtype=torch.uint8, device=dev)   # 2x the 126 MB L2
 
+    from gslam_b200.losses import tracking_loss
+
     def loss_fn(out, gt_):
-        # active-NeRF photometric term of the tracking / mapping steps
-        # (gslam/frontend.py:113-129, gslam/backend.py:277-283)
-        err = out.rgbs - gt_
-        return (err.square().sum(dim=-1) * out.betas.pow(-2.0)).mean()
+        # active-NeRF photometric term of the tracking step (gslam/frontend.py:113-129), fused kernel
+        return tracking_loss(out.render, gt_, None, "active-nerf")
 
     def step(ps, vm_, K_, gt_):
         for p in ps:
@@ -329,6 +329,8 @@ def run_ours(args):
             "gsb_segment_sort": (8 + 8 + 4) * I,
             "gsb_composite_fwd": 52 * I + (4 * 5 + 8) * px,
             "gsb_composite_bwd": 52 * I + (8 * 5 + 12) * px + 48 * I,
+            "gsb_photo_loss": (20 + 12 + 20) * px,
+            "gsb_scale_by_scalar": 40 * px,
         }
         stages = []
         for name, (calls, msk) in sorted(kt.items(), key=lambda kv: -kv[1][1]):
