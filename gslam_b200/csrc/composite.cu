@@ -2,125 +2,157 @@
 // Replaces gsplat rasterize_to_pixels (fork variant with n_touched /
 // visibility_min_T) as called at reference gslam/rasterization.py:325-339.
 //
-// One CTA of 2 warps owns one 16x16 tile of one camera and every thread owns FOUR
-// pixels (slot j of lane l = pixel (l & 7, l >> 3) of the j-th 8x4 block of the
-// warp's 16x8 half-tile), the same layout as the backward kernel.  Four
-// independent pixels per thread amortise the shared-memory reads and the loop
-// overhead and give the scheduler ILP; the small CTA (64 threads, ~60 registers)
-// lets every tile of a 640x480 view be resident in a single wave on 148 SMs.
-// Sorted splat records (48 B) are gathered in batches into shared memory as three
-// float4 planes and read as conflict-free broadcasts.  The conic is pre-scaled by
-// log2(e) at staging so that alpha = opacity * ex2(-sigma') is FMUL + MUFU.EX2.
+// See composite.cuh for the decomposition: one warp per 16x8 half-tile, four
+// pixels per thread, cp.async-staged rounds of 32 list entries, exact per-half-tile
+// culling with ballot compaction.  The warp then walks only the kept entries:
+//   phase 1 (branch-free): sigma', ex2 and alpha of its four pixels;
+//   one ballot per 8x4 slot; slots without a hit are skipped warp-uniformly;
+//   phase 2 (predicated): blend, transmittance update, stop / n_touched bookkeeping.
+// The conic is pre-scaled by log2(e) at staging so alpha = opacity * ex2(-sigma')
+// is one FMUL + MUFU.EX2.
 #include "composite.cuh"
 
-#define FWD_THREADS 64
-#define FWD_BATCH 128
-#define PPT 4
-
 template <bool COUNT, bool STATS>
-__global__ void __launch_bounds__(FWD_THREADS)
+__global__ void __launch_bounds__(CMP_THREADS)
 composite_fwd_kernel(const float4* __restrict__ rec, const int32_t* __restrict__ flatten_ids,
-                     const int32_t* __restrict__ offsets, const float* __restrict__ backgrounds, int C,
-                     int width, int height, int tile_w, int tile_h, int64_t n_isects, float min_T,
-                     float* __restrict__ render, float* __restrict__ alphas,
+                     const int32_t* __restrict__ offsets, const float* __restrict__ backgrounds,
+                     int n_lin, int width, int height, int tile_w, int tile_h, int64_t n_isects,
+                     float min_T, float* __restrict__ render, float* __restrict__ alphas,
                      int32_t* __restrict__ last_ids, int32_t* __restrict__ n_touched,
                      unsigned long long* __restrict__ pair_count) {
-    __shared__ float4 s0[FWD_BATCH];   // x, y, opacity, a'
-    __shared__ float4 s1[FWD_BATCH];   // b', c', r, g
-    __shared__ float4 s2[FWD_BATCH];   // b, depth, beta, -
-    __shared__ int32_t s_id[FWD_BATCH];
-    __shared__ int32_t s_cnt[FWD_BATCH];
-
-    const int cam = blockIdx.z, tile = blockIdx.y * tile_w + blockIdx.x;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int bx = blockIdx.x * GSB_TILE + (lane & 7);
-    const int by = blockIdx.y * GSB_TILE + warp * 8 + (lane >> 3);
+    __shared__ WarpStage s_ws[CMP_WARPS];
+    __shared__ int32_t s_ids[CMP_WARPS][NSTAGE][RND];
+    const unsigned full = 0xffffffffu;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int half_id = blockIdx.x * CMP_WARPS + warp;
+    const int lin = half_id >> 1, half = half_id & 1;     // lin = camera * T + tile
+    if (lin >= n_lin) return;
+    WarpStage& ws = s_ws[warp];
+    const int n_tiles = tile_w * tile_h;
+    const int cam = lin / n_tiles, tile = lin - cam * n_tiles;
+    const int ty = tile / tile_w, tx = tile - ty * tile_w;
+    const int bx = tx * GSB_TILE + (lane & 7);
+    const int by = ty * GSB_TILE + half * 8 + (lane >> 3);
     const float pxf = (float)bx + 0.5f, pyf = (float)by + 0.5f;
+    Rect rc;
+    rc.x0 = (float)(tx * GSB_TILE) + 0.5f; rc.x1 = rc.x0 + 15.0f;
+    rc.y0 = (float)(ty * GSB_TILE + half * 8) + 0.5f; rc.y1 = rc.y0 + 7.0f;
 
-    TileRange rg = tile_range(offsets, cam, tile, tile_w * tile_h, C, n_isects);
+    const TileRange rg = tile_range(offsets, lin, n_lin, n_isects);
     float T[PPT], acc[PPT][GSB_CH];
-    int cur[PPT], visited = 0;
+    int cur[PPT], stop_at[PPT];
     unsigned live = 0;      // bit j: slot j still accumulating
 #pragma unroll
     for (int j = 0; j < PPT; ++j) {
-        T[j] = 1.0f; cur[j] = 0;
+        T[j] = 1.0f; cur[j] = 0; stop_at[j] = -1;
 #pragma unroll
         for (int k = 0; k < GSB_CH; ++k) acc[j][k] = 0.f;
         if (bx + (j & 1) * 8 < width && by + (j >> 1) * 4 < height) live |= 1u << j;
     }
     const unsigned inside = live;
 
-    for (int b0 = rg.start; b0 < rg.end; b0 += FWD_BATCH) {
-        // barrier: everyone is past the previous batch; leave when every pixel is saturated
-        if (__syncthreads_count(live == 0) == FWD_THREADS) break;
-        const int bs = min(FWD_BATCH, rg.end - b0);
-        for (int t = tid; t < bs; t += FWD_THREADS) {
-            const int id = flatten_ids[b0 + t];
-            stage_splat(rec + (size_t)id * 3, s0[t], s1[t], s2[t]);
-            if (COUNT) { s_id[t] = id; s_cnt[t] = 0; }
-        }
-        __syncthreads();
-        for (int t = 0; t < bs; ++t) {
-            if ((t & 7) == 0 && __all_sync(0xffffffffu, live == 0)) break;
-            const float4 g0 = s0[t];        // x, y, a', b'
-            const float4 g1 = s1[t];        // c', thr, opacity, r
-            // Phase 1, branch-free: sigma and alpha of the four pixels (independent chains overlap)
-            const float dx0 = g0.x - pxf, dx1 = dx0 - 8.0f;
-            const float dy0 = g0.y - pyf, dy1 = dy0 - 4.0f;
-            const float ax0 = g0.z * dx0 * dx0, ax1 = g0.z * dx1 * dx1;
-            const float cy0 = g1.x * dy0 * dy0, cy1 = g1.x * dy1 * dy1;
-            const float bx0 = g0.w * dx0, bx1 = g0.w * dx1;
-            float sigma[PPT], alpha[PPT];
-            sigma[0] = fmaf(bx0, dy0, ax0 + cy0);
-            sigma[1] = fmaf(bx1, dy0, ax1 + cy0);
-            sigma[2] = fmaf(bx0, dy1, ax0 + cy1);
-            sigma[3] = fmaf(bx1, dy1, ax1 + cy1);
-            bool hit[PPT];
-            unsigned any = 0;
-#pragma unroll
-            for (int j = 0; j < PPT; ++j) {
-                alpha[j] = fminf(ALPHA_MAX, g1.z * fast_ex2(-sigma[j]));
-                const bool alive = (live >> j) & 1u;
-                if (STATS && alive) ++visited;
-                hit[j] = alive && sigma[j] >= 0.f && alpha[j] >= ALPHA_MIN;
-                any |= hit[j] ? 1u : 0u;
+    const int n = rg.end - rg.start;
+    const int n_rounds = (n + RND - 1) / RND;
+    auto load_id = [&](int r) -> int {
+        const int li = rg.start + r * RND + lane;
+        return (r < n_rounds && li < rg.end) ? flatten_ids[li] : -1;
+    };
+    if (n_rounds > 0) {
+        int id0 = load_id(0), id1 = load_id(1);
+        int id_next = load_id(2);
+        s_ids[warp][0][lane] = id0;
+        issue_round(ws, 0, lane, rec, id0);
+        s_ids[warp][1][lane] = id1;
+        issue_round(ws, 1, lane, rec, id1);
+        int stage = 0;          // ring slot of round r
+        for (int r = 0; r < n_rounds; ++r) {
+            if (__all_sync(full, live == 0)) break;
+            int st2 = stage + 2; if (st2 >= NSTAGE) st2 -= NSTAGE;
+            s_ids[warp][st2][lane] = id_next;
+            issue_round(ws, st2, lane, rec, id_next);
+            id_next = load_id(r + 3);
+            cp_async_wait<2>();
+            __syncwarp();
+            // ---- cull + compact this round's 32 entries ------------------------------------
+            const int li = rg.start + r * RND + lane;
+            int n_keep;
+            {
+                const float4* raw = &ws.raw[stage][lane * 3];
+                float4 o0, o1, o2;
+                const bool keep = (li < rg.end) && stage_and_cull(raw[0], raw[1], raw[2], rc, li, o0, o1, o2);
+                const unsigned m = __ballot_sync(full, keep);
+                n_keep = __popc(m);
+                if (keep) {
+                    const int pos = __popc(m & ((1u << lane) - 1u));
+                    ws.k0[pos] = o0; ws.k1[pos] = o1; ws.k2[pos] = o2;
+                    if (COUNT) ws.gid[pos] = s_ids[warp][stage][lane];
+                }
             }
-            // Phase 2: one vote; most (tile, splat) pairs touch no pixel of this warp's half-tile
-            if (!__any_sync(0xffffffffu, any != 0)) continue;
-            const float4 g2 = s2[t];        // g, b, depth, beta
-            int n_touch = 0;
+            __syncwarp();
+            // ---- composite the kept entries ----------------------------------------------------
+            int cnt_reg = 0;    // lane k: pixels that counted kept entry k as "touched"
+            for (int k = 0; k < n_keep; ++k) {
+                if ((k & 7) == 7 && __all_sync(full, live == 0)) break;
+                const float4 g0 = ws.k0[k];        // x, y, a', b'
+                const float4 g1 = ws.k1[k];        // c', list index, opacity, r
+                const float dx0 = g0.x - pxf, dx1 = dx0 - 8.0f;
+                const float dy0 = g0.y - pyf, dy1 = dy0 - 4.0f;
+                const float ax0 = g0.z * dx0, ax1 = g0.z * dx1;
+                const float cy0 = g1.x * dy0 * dy0, cy1 = g1.x * dy1 * dy1;
+                float sigma[PPT], alpha[PPT];
+                sigma[0] = fmaf(dx0, fmaf(g0.w, dy0, ax0), cy0);
+                sigma[1] = fmaf(dx1, fmaf(g0.w, dy0, ax1), cy0);
+                sigma[2] = fmaf(dx0, fmaf(g0.w, dy1, ax0), cy1);
+                sigma[3] = fmaf(dx1, fmaf(g0.w, dy1, ax1), cy1);
+                bool hit[PPT];
+                unsigned votes[PPT];
 #pragma unroll
-            for (int j = 0; j < PPT; ++j) {
-                // predicated, no divergence: a miss composites alpha = 0
-                const float al = hit[j] ? alpha[j] : 0.f;
-                const float next_T = T[j] * (1.0f - al);
-                const bool stop = hit[j] && next_T <= T_STOP;
-                const bool take = hit[j] && !stop;
-                const float vis = take ? al * T[j] : 0.f;
-                acc[j][0] = fmaf(g1.w, vis, acc[j][0]);
-                acc[j][1] = fmaf(g2.x, vis, acc[j][1]);
-                acc[j][2] = fmaf(g2.y, vis, acc[j][2]);
-                acc[j][3] = fmaf(g2.z, vis, acc[j][3]);
-                acc[j][4] = fmaf(g2.w, vis, acc[j][4]);
-                const bool touched = take && T[j] > min_T;
-                cur[j] = take ? b0 + t : cur[j];
-                T[j] = take ? next_T : T[j];
-                if (stop) live &= ~(1u << j);
-                if (COUNT) n_touch += __popc(__ballot_sync(0xffffffffu, touched));
+                for (int j = 0; j < PPT; ++j) {
+                    alpha[j] = fminf(ALPHA_MAX, g1.z * fast_ex2(-sigma[j]));
+                    hit[j] = ((live >> j) & 1u) && sigma[j] >= 0.f && alpha[j] >= ALPHA_MIN;
+                }
+#pragma unroll
+                for (int j = 0; j < PPT; ++j) votes[j] = __ballot_sync(full, hit[j]);
+                if ((votes[0] | votes[1] | votes[2] | votes[3]) == 0u) continue;
+                const float4 g2 = ws.k2[k];        // g, b, depth, beta
+                const int idx = __float_as_int(g1.y);
+                int n_touch = 0;
+#pragma unroll
+                for (int j = 0; j < PPT; ++j) {
+                    if (votes[j] == 0u) continue;              // warp-uniform
+                    // predicated, no divergence: a miss composites alpha = 0
+                    const float al = hit[j] ? alpha[j] : 0.f;
+                    const float next_T = T[j] * (1.0f - al);
+                    const bool stop = hit[j] && next_T <= T_STOP;
+                    const bool take = hit[j] && !stop;
+                    const float vis = take ? al * T[j] : 0.f;
+                    acc[j][0] = fmaf(g1.w, vis, acc[j][0]);
+                    acc[j][1] = fmaf(g2.x, vis, acc[j][1]);
+                    acc[j][2] = fmaf(g2.y, vis, acc[j][2]);
+                    acc[j][3] = fmaf(g2.z, vis, acc[j][3]);
+                    acc[j][4] = fmaf(g2.w, vis, acc[j][4]);
+                    if (COUNT) n_touch += __popc(__ballot_sync(full, take && T[j] > min_T));
+                    cur[j] = take ? idx : cur[j];
+                    T[j] = take ? next_T : T[j];
+                    if (stop) {
+                        live &= ~(1u << j);
+                        if (STATS) stop_at[j] = idx;
+                    }
+                }
+                if (COUNT && lane == k) cnt_reg = n_touch;
             }
-            if (COUNT && n_touch && lane == 0) atomicAdd(&s_cnt[t], n_touch);
+            if (COUNT && cnt_reg > 0) atomicAdd(n_touched + ws.gid[lane], cnt_reg);
+            __syncwarp();
+            if (++stage == NSTAGE) stage = 0;
         }
-        if (COUNT) {
-            __syncthreads();
-            for (int t = tid; t < bs; t += FWD_THREADS)
-                if (s_cnt[t] > 0) atomicAdd(n_touched + s_id[t], s_cnt[t]);
-        }
+        cp_async_wait<0>();
     }
     float bg[GSB_CH] = {0.f, 0.f, 0.f, 0.f, 0.f};
     if (backgrounds) {
 #pragma unroll
         for (int k = 0; k < GSB_CH; ++k) bg[k] = backgrounds[cam * GSB_CH + k];
     }
+    int visited = 0;
 #pragma unroll
     for (int j = 0; j < PPT; ++j) {
         if (!((inside >> j) & 1u)) continue;
@@ -130,9 +162,11 @@ composite_fwd_kernel(const float4* __restrict__ rec, const int32_t* __restrict__
         for (int k = 0; k < GSB_CH; ++k) render[pix * GSB_CH + k] = acc[j][k] + T[j] * bg[k];
         alphas[pix] = 1.0f - T[j];
         last_ids[pix] = cur[j];
+        // P: entries walked while the pixel was still accumulating (the stopping one included)
+        if (STATS) visited += stop_at[j] >= 0 ? stop_at[j] - rg.start + 1 : n;
     }
     if (STATS) {
-        int v = __reduce_add_sync(0xffffffffu, visited);
+        int v = __reduce_add_sync(full, visited);
         if (lane == 0 && v) atomicAdd(pair_count, (unsigned long long)v);
     }
 }
@@ -147,13 +181,17 @@ GSB_API int gsb_composite_fwd(const float* rec, const int32_t* flatten_ids, cons
     if (C == 0) return 0;
     GSB_CHECK_ARG(offsets && render && alphas && last_ids);
     GSB_CHECK_ARG(n_isects <= 0 || (rec && flatten_ids));
-    GSB_CHECK_ARG(n_isects < ((int64_t)1 << 31) && C <= 65535);
-    dim3 grid(tile_w, tile_h, C);
+    GSB_CHECK_ARG(n_isects < ((int64_t)1 << 31));
+    GSB_CHECK_ARG(tile_w == (width + GSB_TILE - 1) / GSB_TILE && tile_h == (height + GSB_TILE - 1) / GSB_TILE);
+    const int64_t n_lin64 = (int64_t)C * tile_w * tile_h;
+    GSB_CHECK_ARG(n_lin64 * 2 < ((int64_t)1 << 31));
+    const int n_lin = (int)n_lin64;
+    const int grid = (2 * n_lin + CMP_WARPS - 1) / CMP_WARPS;
     const float4* r4 = reinterpret_cast<const float4*>(rec);
     unsigned long long* pc = reinterpret_cast<unsigned long long*>(pair_count);
 #define GSB_FWD(COUNT, STATS)                                                                     \
-    composite_fwd_kernel<COUNT, STATS><<<grid, FWD_THREADS, 0, gsb_stream(stream)>>>(             \
-        r4, flatten_ids, offsets, backgrounds, C, width, height, tile_w, tile_h, n_isects,        \
+    composite_fwd_kernel<COUNT, STATS><<<grid, CMP_THREADS, 0, gsb_stream(stream)>>>(             \
+        r4, flatten_ids, offsets, backgrounds, n_lin, width, height, tile_w, tile_h, n_isects,    \
         visibility_min_T, render, alphas, last_ids, n_touched, pc)
     if (n_touched && pc) GSB_FWD(true, true);
     else if (n_touched) GSB_FWD(true, false);
@@ -163,4 +201,3 @@ GSB_API int gsb_composite_fwd(const float* rec, const int32_t* flatten_ids, cons
     GSB_LAUNCH_CHECK();
     return 0;
 }
-

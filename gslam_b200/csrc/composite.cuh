@@ -1,38 +1,112 @@
 // Definitions shared by the compositing forward and backward kernels.
+//
+// Work decomposition (both directions): ONE WARP owns one 16x8 half-tile and walks the
+// tile's depth-sorted list on its own -- no CTA barrier anywhere.  Every thread owns FOUR
+// pixels: slot j of lane l is pixel (l & 7, l >> 3) of the j-th 8x4 block of the half-tile.
+//
+// The list is consumed in rounds of 32 entries.  Splat records (48 B) are gathered
+// from HBM/L2 into a three-stage shared-memory ring with cp.async (LDGSTS, 3 x 16 B per
+// lane), two rounds ahead of use; the ids that address them are prefetched one round
+// earlier still.  When a round lands, every lane takes one record, pre-scales the
+// conic by log2(e), and runs an EXACT ellipse-vs-rectangle test: the minimum of the
+// quadratic form over the half-tile's pixel-centre rectangle is compared with
+// log2(255 * opacity), the largest exponent that can still reach alpha >= 1/255.
+// Entries that cannot touch the half-tile (about half of gsplat's 3-sigma bounding-
+// square list) are dropped by a ballot/popc compaction, so the per-pixel loop only
+// sees splats that matter.
 #pragma once
 #include "common.cuh"
 
-#define BATCH 256
 #define ALPHA_MAX 0.999f
 #define ALPHA_MIN (1.0f / 255.0f)
 #define T_STOP 1e-4f
 #define LOG2E 1.4426950408889634f
 
+#define CMP_WARPS 2            // independent half-tile workers per CTA
+#define CMP_THREADS (32 * CMP_WARPS)
+#define RND 32                 // list entries per round (one per lane)
+#define NSTAGE 3               // cp.async ring depth
+#define PPT 4                  // pixels per thread
+
 struct TileRange {
     int start, end;
 };
 
-__device__ __forceinline__ TileRange tile_range(const int32_t* offsets, int cam, int tile, int n_tiles,
-                                                int C, int64_t n_isects) {
+__device__ __forceinline__ TileRange tile_range(const int32_t* offsets, int lin, int n_lin,
+                                                int64_t n_isects) {
     TileRange r;
-    int lin = cam * n_tiles + tile;
     r.start = offsets[lin];
     // n_isects < 0: offsets has C*T+1 entries (device-side count, gsb_tile_scan)
-    r.end = (lin == C * n_tiles - 1 && n_isects >= 0) ? (int)n_isects : offsets[lin + 1];
+    r.end = (lin == n_lin - 1 && n_isects >= 0) ? (int)n_isects : offsets[lin + 1];
     return r;
 }
 
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gmem_src) {
+    unsigned s = (unsigned)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s), "l"(gmem_src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+    asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
 
-// Shared-memory staging layout of one splat (three float4 planes):
-//   s0 = {x, y, a', b'}   s1 = {c', thr, opacity, r}   s2 = {g, b, depth, beta}
-// a', b', c' is the conic pre-scaled so that sigma' = a'dx^2 + b'dxdy + c'dy^2 = sigma * log2(e);
-// thr = log2(255 * opacity) + margin: pairs with sigma' > thr cannot reach alpha >= 1/255, so the
-// inner loops reject them on sigma' alone (no MUFU); pairs that pass still take the exact test.
-#define THR_MARGIN 1e-3f
-__device__ __forceinline__ void stage_splat(const float4* __restrict__ rp, float4& o0, float4& o1,
-                                            float4& o2) {
-    const float4 r0 = rp[0], r1 = rp[1], r2 = rp[2];
-    o0 = make_float4(r0.x, r0.y, r0.w * (0.5f * LOG2E), r1.x * LOG2E);
-    o1 = make_float4(r1.y * (0.5f * LOG2E), __log2f(255.0f * r0.z) + THR_MARGIN, r0.z, r1.z);
+// Per-warp staging area.
+struct __align__(16) WarpStage {
+    float4 raw[NSTAGE][RND * 3];   // ring of gathered records, lane-major (48 B per lane)
+    float4 k0[RND];                // kept entries: x, y, a', b'
+    float4 k1[RND];                //               c', list index (int bits), opacity, r
+    float4 k2[RND];                //               g, b, depth, beta
+    int32_t gid[RND];              //               flatten id (camera * N + gaussian)
+};
+
+// The half-tile's pixel-centre rectangle.
+struct Rect {
+    float x0, x1, y0, y1;
+};
+
+// One staged record -> compaction planes, plus the cull decision.
+// a', b', c' is the conic pre-scaled so that sigma' = a'dx^2 + b'dxdy + c'dy^2 = sigma * log2(e).
+__device__ __forceinline__ bool stage_and_cull(const float4 r0, const float4 r1, const float4 r2,
+                                               const Rect rc, int list_index, float4& o0, float4& o1,
+                                               float4& o2) {
+    const float x = r0.x, y = r0.y, op = r0.z;
+    const float A = r0.w * (0.5f * LOG2E), B = r1.x * LOG2E, Cc = r1.y * (0.5f * LOG2E);
+    o0 = make_float4(x, y, A, B);
+    o1 = make_float4(Cc, __int_as_float(list_index), op, r1.z);
     o2 = make_float4(r1.w, r2.x, r2.y, r2.z);
+    // dx = x - px ranges over [dxl, dxh], dy likewise
+    const float dxl = x - rc.x1, dxh = x - rc.x0, dyl = y - rc.y1, dyh = y - rc.y0;
+    if (dxl <= 0.f && dxh >= 0.f && dyl <= 0.f && dyh >= 0.f) return true;   // centre inside
+    // outside: the minimum of the (positive definite) form lies on the boundary; take each edge's
+    // 1-D minimiser clamped to the edge
+    const float hA = 0.5f * fast_rcp(A), hC = 0.5f * fast_rcp(Cc);
+    float q = 3.0e38f;
+    {
+        const float dy0 = fminf(fmaxf(-B * dxl * hC, dyl), dyh);
+        q = fminf(q, fmaf(dxl, fmaf(A, dxl, B * dy0), Cc * dy0 * dy0));
+        const float dy1 = fminf(fmaxf(-B * dxh * hC, dyl), dyh);
+        q = fminf(q, fmaf(dxh, fmaf(A, dxh, B * dy1), Cc * dy1 * dy1));
+        const float dx0 = fminf(fmaxf(-B * dyl * hA, dxl), dxh);
+        q = fminf(q, fmaf(dx0, fmaf(A, dx0, B * dyl), Cc * dyl * dyl));
+        const float dx1 = fminf(fmaxf(-B * dyh * hA, dxl), dxh);
+        q = fminf(q, fmaf(dx1, fmaf(A, dx1, B * dyh), Cc * dyh * dyh));
+    }
+    // alpha >= 1/255 needs sigma' <= log2(255 * opacity); the margin covers the rounding of the
+    // per-pixel evaluation (cancellation in very anisotropic conics included)
+    const float dxm = fmaxf(fabsf(dxl), fabsf(dxh)), dym = fmaxf(fabsf(dyl), fabsf(dyh));
+    const float margin = 1e-3f + 4e-6f * (A * dxm * dxm + fabsf(B) * dxm * dym + Cc * dym * dym);
+    return q <= __log2f(255.0f * op) + margin;
+}
+
+// Issue the gather of one round: lane copies the 48-byte record `id` into raw[stage][lane*3..].
+__device__ __forceinline__ void issue_round(WarpStage& ws, int stage, int lane, const float4* rec, int id) {
+    if (id >= 0) {
+        const float4* src = rec + (size_t)id * 3;
+        float4* dst = &ws.raw[stage][lane * 3];
+        cp_async16(dst, src);
+        cp_async16(dst + 1, src + 1);
+        cp_async16(dst + 2, src + 2);
+    }
+    cp_async_commit();
 }

@@ -5,22 +5,19 @@
 // transmittance is rebuilt by dividing T_final by (1 - alpha), the colour behind
 // each splat is a running suffix sum.
 //
-// Layout: one CTA of 2 warps per 16x16 tile, FOUR pixels per thread.  Warp w owns
-// the 16x8 half-tile; pixel slot j of lane l is pixel (l & 7, l >> 3) of the j-th
-// 8x4 block of that half.  Consequences:
+// Same decomposition as the forward kernel (composite.cuh): one independent warp per
+// 16x8 half-tile, FOUR pixels per thread, cp.async-staged rounds of 32 entries that are
+// culled against the half-tile and compacted before the per-pixel loop.  Consequences:
 //   * a thread sums the gradients of its 4 pixels in registers before any
 //     cross-lane traffic, so the warp reduction runs once per 128 pixels;
 //   * a slot is a compact 8x4 block, so small splats leave whole slots without a
 //     hit and the warp skips their gradient math after one vote;
 //   * the reduction is a transposing butterfly: 16 values over 32 lanes in
 //     8+4+2+1+1 = 16 shuffles (a plain butterfly needs 11 x 5 = 55), after which
-//     16 lanes each hold one finished sum and add it to shared memory in parallel;
-//   * per (tile, Gaussian) the CTA issues three float4 atomics to v_rec.
+//     16 lanes each hold one finished sum and park it in the warp's shared-memory row;
+//   * per (half-tile, kept Gaussian) one lane issues three float4 atomics to v_rec,
+//     32 Gaussians at a time.
 #include "composite.cuh"
-
-#define BWD_THREADS 64
-#define BWD_BATCH 128
-#define PPT 4
 
 // Sum v[0..15] over the warp.  On return lane l holds in `out` the total of value
 // index idx(l) = 8*b4 + 4*b3 + 2*b2 + b1 (b_k = bit k of l); lanes l and l^1 agree.
@@ -55,30 +52,35 @@ __device__ __forceinline__ float transpose_reduce16(const float (&v)[16], int la
     return d;
 }
 
-// 9 CTAs per SM (<= 113 registers): 148 x 9 = 1332 slots hold all 1200 tiles of a 640x480 view in
-// one wave; at 8 per SM the last 16 tiles ran as a second wave on an otherwise idle GPU.
-__global__ void __launch_bounds__(BWD_THREADS, 9)
+__global__ void __maxnreg__(112)
 composite_bwd_kernel(const float4* __restrict__ rec, const int32_t* __restrict__ flatten_ids,
-                     const int32_t* __restrict__ offsets, const float* __restrict__ backgrounds, int C,
-                     int width, int height, int tile_w, int tile_h, int64_t n_isects,
+                     const int32_t* __restrict__ offsets, const float* __restrict__ backgrounds,
+                     int n_lin, int width, int height, int tile_w, int tile_h, int64_t n_isects,
                      const float* __restrict__ render_alphas, const int32_t* __restrict__ last_ids,
                      const float* __restrict__ v_render, const float* __restrict__ v_alphas,
                      float* __restrict__ v_rec, float* __restrict__ v_backgrounds) {
-    __shared__ float4 s0[BWD_BATCH];   // x, y, opacity, a'   (conic pre-scaled as in the forward pass)
-    __shared__ float4 s1[BWD_BATCH];   // b', c', r, g
-    __shared__ float4 s2[BWD_BATCH];   // b, depth, beta, -
-    __shared__ int32_t s_id[BWD_BATCH];
-    __shared__ __align__(16) float s_acc[BWD_BATCH][16];
-    __shared__ int s_max[2];
-
-    const int cam = blockIdx.z, tile = blockIdx.y * tile_w + blockIdx.x;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    __shared__ WarpStage s_ws[CMP_WARPS];
+    __shared__ int32_t s_ids[CMP_WARPS][NSTAGE][RND];
+    __shared__ __align__(16) float s_acc[CMP_WARPS][RND][12];
+    const unsigned full = 0xffffffffu;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int half_id = blockIdx.x * CMP_WARPS + warp;
+    const int lin = half_id >> 1, half = half_id & 1;
+    if (lin >= n_lin) return;
+    WarpStage& ws = s_ws[warp];
+    float (*acc_rows)[12] = s_acc[warp];
+    const int n_tiles = tile_w * tile_h;
+    const int cam = lin / n_tiles, tile = lin - cam * n_tiles;
+    const int ty = tile / tile_w, tx = tile - ty * tile_w;
     // slot j -> pixel (bx + (j & 1) * 8, by + (j >> 1) * 4)
-    const int bx = blockIdx.x * GSB_TILE + (lane & 7);
-    const int by = blockIdx.y * GSB_TILE + warp * 8 + (lane >> 3);
+    const int bx = tx * GSB_TILE + (lane & 7);
+    const int by = ty * GSB_TILE + half * 8 + (lane >> 3);
     const float pxf = (float)bx + 0.5f, pyf = (float)by + 0.5f;
+    Rect rc;
+    rc.x0 = (float)(tx * GSB_TILE) + 0.5f; rc.x1 = rc.x0 + 15.0f;
+    rc.y0 = (float)(ty * GSB_TILE + half * 8) + 0.5f; rc.y1 = rc.y0 + 7.0f;
 
-    TileRange rg = tile_range(offsets, cam, tile, tile_w * tile_h, C, n_isects);
+    const TileRange rg = tile_range(offsets, lin, n_lin, n_isects);
 
     float T[PPT], tail[PPT], vr[PPT][GSB_CH], buf[PPT][GSB_CH];
     int bin_final[PPT];
@@ -123,46 +125,60 @@ composite_bwd_kernel(const float4* __restrict__ rec, const int32_t* __restrict__
             if (lane == 0 && s != 0.f) atomicAdd(v_backgrounds + cam * GSB_CH + k, s);
         }
     }
-    const int warp_last = __reduce_max_sync(0xffffffffu, my_last);
-    int slot_last[PPT];
-#pragma unroll
-    for (int j = 0; j < PPT; ++j) slot_last[j] = __reduce_max_sync(0xffffffffu, bin_final[j]);
-    if (lane == 0) s_max[warp] = warp_last;
-    __syncthreads();
-    const int block_last = max(s_max[0], s_max[1]);
-    if (block_last < rg.start || rg.end <= rg.start) return;
+    const int warp_last = __reduce_max_sync(full, my_last);
+    if (warp_last < rg.start || rg.end <= rg.start) return;
 
-    const int range_end = min(rg.end, block_last + 1);
-    const int n_batches = (range_end - rg.start + BWD_BATCH - 1) / BWD_BATCH;
-    for (int b = n_batches - 1; b >= 0; --b) {
-        const int b0 = rg.start + b * BWD_BATCH;
-        const int bs = min(BWD_BATCH, range_end - b0);
-        __syncthreads();
-        for (int t = tid; t < bs; t += BWD_THREADS) {
-            const int id = flatten_ids[b0 + t];
-            stage_splat(rec + (size_t)id * 3, s0[t], s1[t], s2[t]);
-            s_id[t] = id;
-        }
+    const int range_end = min(rg.end, warp_last + 1);
+    const int n_rounds = (range_end - rg.start + RND - 1) / RND;
+    auto load_id = [&](int r) -> int {          // rounds are walked from the back
+        const int li = rg.start + r * RND + lane;
+        return (r >= 0 && li < range_end) ? flatten_ids[li] : -1;
+    };
+    int id0 = load_id(n_rounds - 1), id1 = load_id(n_rounds - 2);
+    int id_next = load_id(n_rounds - 3);
+    s_ids[warp][0][lane] = id0;
+    issue_round(ws, 0, lane, rec, id0);
+    s_ids[warp][1][lane] = id1;
+    issue_round(ws, 1, lane, rec, id1);
+    int stage = 0;
+    for (int r = n_rounds - 1; r >= 0; --r) {
+        int st2 = stage + 2; if (st2 >= NSTAGE) st2 -= NSTAGE;
+        s_ids[warp][st2][lane] = id_next;
+        issue_round(ws, st2, lane, rec, id_next);
+        id_next = load_id(r - 3);
+        cp_async_wait<2>();
+        __syncwarp();
+        // ---- cull + compact ---------------------------------------------------------------
+        const int li = rg.start + r * RND + lane;
+        int n_keep;
         {
-            float4* z = reinterpret_cast<float4*>(&s_acc[0][0]);
-            for (int t = tid; t < bs * 4; t += BWD_THREADS) z[t] = make_float4(0.f, 0.f, 0.f, 0.f);
+            const float4* raw = &ws.raw[stage][lane * 3];
+            float4 o0, o1, o2;
+            const bool keep = (li < range_end) && stage_and_cull(raw[0], raw[1], raw[2], rc, li, o0, o1, o2);
+            const unsigned m = __ballot_sync(full, keep);
+            n_keep = __popc(m);
+            if (keep) {
+                const int pos = __popc(m & ((1u << lane) - 1u));
+                ws.k0[pos] = o0; ws.k1[pos] = o1; ws.k2[pos] = o2;
+                ws.gid[pos] = s_ids[warp][stage][lane];
+            }
         }
-        __syncthreads();
-        for (int t = min(bs - 1, warp_last - b0); t >= 0; --t) {
-            const int idx = b0 + t;
-            const float4 g0 = s0[t];        // x, y, a', b'
-            const float4 g1 = s1[t];        // c', thr, opacity, r
+        __syncwarp();
+        unsigned wrote = 0;      // bit k: kept entry k produced a gradient row
+        for (int k = n_keep - 1; k >= 0; --k) {
+            const float4 g0 = ws.k0[k];        // x, y, a', b'
+            const float4 g1 = ws.k1[k];        // c', list index, opacity, r
+            const int idx = __float_as_int(g1.y);
             // Phase 1, branch-free: sigma', exp and alpha of the four pixels (chains overlap)
             const float dx0 = g0.x - pxf, dx1 = dx0 - 8.0f;
             const float dy0 = g0.y - pyf, dy1 = dy0 - 4.0f;
-            const float ax0 = g0.z * dx0 * dx0, ax1 = g0.z * dx1 * dx1;
+            const float ax0 = g0.z * dx0, ax1 = g0.z * dx1;
             const float cy0 = g1.x * dy0 * dy0, cy1 = g1.x * dy1 * dy1;
-            const float bx0 = g0.w * dx0, bx1 = g0.w * dx1;
             float sigma[PPT], vis[PPT], alpha[PPT];
-            sigma[0] = fmaf(bx0, dy0, ax0 + cy0);
-            sigma[1] = fmaf(bx1, dy0, ax1 + cy0);
-            sigma[2] = fmaf(bx0, dy1, ax0 + cy1);
-            sigma[3] = fmaf(bx1, dy1, ax1 + cy1);
+            sigma[0] = fmaf(dx0, fmaf(g0.w, dy0, ax0), cy0);
+            sigma[1] = fmaf(dx1, fmaf(g0.w, dy0, ax1), cy0);
+            sigma[2] = fmaf(dx0, fmaf(g0.w, dy1, ax0), cy1);
+            sigma[3] = fmaf(dx1, fmaf(g0.w, dy1, ax1), cy1);
             bool valid[PPT];
             unsigned votes[PPT];
 #pragma unroll
@@ -172,13 +188,13 @@ composite_bwd_kernel(const float4* __restrict__ rec, const int32_t* __restrict__
                 valid[j] = idx <= bin_final[j] && sigma[j] >= 0.f && alpha[j] >= ALPHA_MIN;
             }
 #pragma unroll
-            for (int j = 0; j < PPT; ++j) votes[j] = __ballot_sync(0xffffffffu, valid[j]);
+            for (int j = 0; j < PPT; ++j) votes[j] = __ballot_sync(full, valid[j]);
             if ((votes[0] | votes[1] | votes[2] | votes[3]) == 0u) continue;
-            const float4 g2 = s2[t];        // g, b, depth, beta
+            const float4 g2 = ws.k2[k];        // g, b, depth, beta
             const float col[GSB_CH] = {g1.w, g2.x, g2.y, g2.z, g2.w};
             float g[16];
 #pragma unroll
-            for (int k = 0; k < 16; ++k) g[k] = 0.f;
+            for (int q = 0; q < 16; ++q) g[q] = 0.f;
             // Phase 2: per 8x4 block, a warp-uniform branch; inside, misses are predicated (alpha = 0)
 #pragma unroll
             for (int j = 0; j < PPT; ++j) {
@@ -190,16 +206,17 @@ composite_bwd_kernel(const float4* __restrict__ rec, const int32_t* __restrict__
                 const float fac = al * Tn;
                 float v_alpha = tail[j] * ra;
 #pragma unroll
-                for (int k = 0; k < GSB_CH; ++k) {
-                    g[6 + k] = fmaf(fac, vr[j][k], g[6 + k]);
-                    v_alpha = fmaf(fmaf(col[k], Tn, -buf[j][k] * ra), vr[j][k], v_alpha);
-                    buf[j][k] = fmaf(col[k], fac, buf[j][k]);
+                for (int q = 0; q < GSB_CH; ++q) {
+                    g[6 + q] = fmaf(fac, vr[j][q], g[6 + q]);
+                    v_alpha = fmaf(fmaf(col[q], Tn, -buf[j][q] * ra), vr[j][q], v_alpha);
+                    buf[j][q] = fmaf(col[q], fac, buf[j][q]);
                 }
                 T[j] = Tn;
                 const float ov = g1.z * vis[j];
                 const float v_sigma = (valid[j] && ov <= ALPHA_MAX) ? -ov * v_alpha : 0.f;
                 const float v_op = (valid[j] && ov <= ALPHA_MAX) ? vis[j] * v_alpha : 0.f;
                 const float vsp = v_sigma * (1.0f / LOG2E);
+                // d sigma'/d(x,y) with sigma' = a'dx^2 + b'dxdy + c'dy^2
                 g[0] = fmaf(vsp, 2.f * g0.z * dx + g0.w * dy, g[0]);
                 g[1] = fmaf(vsp, g0.w * dx + 2.f * g1.x * dy, g[1]);
                 g[2] += v_op;
@@ -209,23 +226,22 @@ composite_bwd_kernel(const float4* __restrict__ rec, const int32_t* __restrict__
             }
             int slot;
             const float total = transpose_reduce16(g, lane, slot);
-            if (!(lane & 1) && slot < 11 && total != 0.f) atomicAdd(&s_acc[t][slot], total);
+            if (!(lane & 1) && slot < 12) acc_rows[k][slot] = total;     // slot 11 is always 0
+            wrote |= 1u << k;
         }
-        __syncthreads();
-        for (int t = tid; t < bs; t += BWD_THREADS) {
-            const float4* a = reinterpret_cast<const float4*>(&s_acc[t][0]);
+        __syncwarp();
+        if ((wrote >> lane) & 1u) {
+            const float4* a = reinterpret_cast<const float4*>(&acc_rows[lane][0]);
             const float4 a0 = a[0], a1 = a[1], a2 = a[2];
-            const bool nz = a0.x != 0.f || a0.y != 0.f || a0.z != 0.f || a0.w != 0.f || a1.x != 0.f ||
-                            a1.y != 0.f || a1.z != 0.f || a1.w != 0.f || a2.x != 0.f || a2.y != 0.f ||
-                            a2.z != 0.f;
-            if (nz) {
-                float4* dst = reinterpret_cast<float4*>(v_rec) + (size_t)s_id[t] * 3;
-                atomicAdd(dst, a0);
-                atomicAdd(dst + 1, a1);
-                atomicAdd(dst + 2, a2);
-            }
+            float4* dst = reinterpret_cast<float4*>(v_rec) + (size_t)ws.gid[lane] * 3;
+            atomicAdd(dst, a0);
+            atomicAdd(dst + 1, a1);
+            atomicAdd(dst + 2, a2);
         }
+        __syncwarp();
+        if (++stage == NSTAGE) stage = 0;
     }
+    cp_async_wait<0>();
 }
 
 GSB_API int gsb_composite_bwd(const float* rec, const int32_t* flatten_ids, const int32_t* offsets,
@@ -237,11 +253,15 @@ GSB_API int gsb_composite_bwd(const float* rec, const int32_t* flatten_ids, cons
     GSB_CHECK_ARG(C >= 0 && width > 0 && height > 0 && tile_w > 0 && tile_h > 0);
     if (C == 0 || n_isects == 0) return 0;
     GSB_CHECK_ARG(rec && flatten_ids && offsets && render_alphas && last_ids && v_render && v_rec);
-    GSB_CHECK_ARG(n_isects < ((int64_t)1 << 31) && C <= 65535);
-    dim3 grid(tile_w, tile_h, C);
-    composite_bwd_kernel<<<grid, BWD_THREADS, 0, gsb_stream(stream)>>>(
-        reinterpret_cast<const float4*>(rec), flatten_ids, offsets, backgrounds, C, width, height, tile_w,
-        tile_h, n_isects, render_alphas, last_ids, v_render, v_alphas, v_rec, v_backgrounds);
+    GSB_CHECK_ARG(n_isects < ((int64_t)1 << 31));
+    GSB_CHECK_ARG(tile_w == (width + GSB_TILE - 1) / GSB_TILE && tile_h == (height + GSB_TILE - 1) / GSB_TILE);
+    const int64_t n_lin64 = (int64_t)C * tile_w * tile_h;
+    GSB_CHECK_ARG(n_lin64 * 2 < ((int64_t)1 << 31));
+    const int n_lin = (int)n_lin64;
+    const int grid = (2 * n_lin + CMP_WARPS - 1) / CMP_WARPS;
+    composite_bwd_kernel<<<grid, CMP_THREADS, 0, gsb_stream(stream)>>>(
+        reinterpret_cast<const float4*>(rec), flatten_ids, offsets, backgrounds, n_lin, width, height,
+        tile_w, tile_h, n_isects, render_alphas, last_ids, v_render, v_alphas, v_rec, v_backgrounds);
     GSB_LAUNCH_CHECK();
     return 0;
 }
