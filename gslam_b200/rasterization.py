@@ -195,3 +195,26 @@ def get_new_splat_depth(
         if packed:
             return ops.pack_visible(radii, means2d, rec)
         return radii, means2d, rec[..., 9]
+
+
+def quat_scale_to_covar_preci(quats: Tensor, scales: Tensor, compute_covar: bool = True,
+                              compute_preci: bool = True, triu: bool = False):
+    """Shim of ``gsplat.quat_scale_to_covar_preci`` (reference gslam/insertion.py:88-91; a few
+    thousand rows every 200 steps, so plain torch ops on the caller's device, not a kernel):
+    covar = R diag(s^2) R^T, preci = R diag(s^-2) R^T with R from the normalised wxyz quaternion."""
+    if triu:
+        _unsupported("quat_scale_to_covar_preci(triu=True)")
+    q = torch.nn.functional.normalize(quats, dim=-1)
+    w, x, y, z = q.unbind(-1)
+    R = torch.stack([
+        1 - 2 * (y * y + z * z), 2 * (x * y - w * z), 2 * (x * z + w * y),
+        2 * (x * y + w * z), 1 - 2 * (x * x + z * z), 2 * (y * z - w * x),
+        2 * (x * z - w * y), 2 * (y * z + w * x), 1 - 2 * (x * x + y * y)], dim=-1).reshape(q.shape[:-1] + (3, 3))
+    covar = preci = None
+    if compute_covar:
+        M = R * scales[..., None, :]
+        covar = M @ M.transpose(-1, -2)
+    if compute_preci:
+        P = R * (1.0 / scales[..., None, :])
+        preci = P @ P.transpose(-1, -2)
+    return covar, preci

@@ -224,3 +224,14 @@ def test_opacity_decay_mask():
     lo = torch.ones(4)
     radii = torch.tensor([[1, 0, 3, 0], [2, 0, 0, 5], [0, 0, 4, 0]])
     assert R.opacity_decay(lo, radii, 0.5).tolist() == [0.5, 1.0, 0.5, 1.0]       # seen in > 1 view only
+
+
+def test_quat_scale_to_covar_preci_shim_matches_oracle():
+    """The torch shim of gsplat.quat_scale_to_covar_preci (gslam/insertion.py:88) vs the oracle's covariance."""
+    from gslam_b200.rasterization import quat_scale_to_covar_preci
+    g = torch.Generator().manual_seed(3)
+    q = torch.rand(64, 4, generator=g)
+    s = torch.rand(64, 3, generator=g) + 0.05
+    covar, preci = quat_scale_to_covar_preci(q, s)
+    assert torch.allclose(covar, R.quat_scale_to_covar(q, s), atol=1e-6)
+    assert torch.allclose(covar @ preci, torch.eye(3).expand(64, 3, 3), atol=1e-4)
