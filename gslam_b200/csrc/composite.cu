@@ -2,10 +2,10 @@
 // Replaces gsplat rasterize_to_pixels (fork variant with n_touched /
 // visibility_min_T) as called at reference gslam/rasterization.py:325-339.
 //
-// See composite.cuh for the decomposition: one warp per 16x8 half-tile, four
-// pixels per thread, cp.async-staged rounds of 32 list entries, exact per-half-tile
+// See composite.cuh for the decomposition: one warp per 8x8 quarter-tile, two
+// pixels per thread, cp.async-staged rounds of 32 list entries, exact per-unit
 // culling with ballot compaction.  The warp then walks only the kept entries:
-//   phase 1 (branch-free): sigma', ex2 and alpha of its four pixels;
+//   phase 1 (branch-free): sigma', ex2 and alpha of its pixels;
 //   one ballot per 8x4 slot; slots without a hit are skipped warp-uniformly;
 //   phase 2 (predicated): blend, transmittance update, stop / n_touched bookkeeping.
 // The conic is pre-scaled by log2(e) at staging so alpha = opacity * ex2(-sigma')
@@ -24,32 +24,32 @@ composite_fwd_kernel(const float4* __restrict__ rec, const int32_t* __restrict__
     __shared__ int32_t s_ids[CMP_WARPS][NSTAGE][RND];
     const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int half_id = blockIdx.x * CMP_WARPS + warp;
-    const int lin = half_id >> 1, half = half_id & 1;     // lin = camera * T + tile
-    if (lin >= n_lin) return;
+    const int unit = blockIdx.x * CMP_WARPS + warp;
+    if (unit >= n_lin * UNITS_PER_TILE) return;
+    const Unit u = decode_unit(unit, lane, tile_w, tile_w * tile_h);
     WarpStage& ws = s_ws[warp];
-    const int n_tiles = tile_w * tile_h;
-    const int cam = lin / n_tiles, tile = lin - cam * n_tiles;
-    const int ty = tile / tile_w, tx = tile - ty * tile_w;
-    const int bx = tx * GSB_TILE + (lane & 7);
-    const int by = ty * GSB_TILE + half * 8 + (lane >> 3);
-    const float pxf = (float)bx + 0.5f, pyf = (float)by + 0.5f;
-    Rect rc;
-    rc.x0 = (float)(tx * GSB_TILE) + 0.5f; rc.x1 = rc.x0 + 15.0f;
-    rc.y0 = (float)(ty * GSB_TILE + half * 8) + 0.5f; rc.y1 = rc.y0 + 7.0f;
+    const float pxf = (float)u.bx + 0.5f, pyf = (float)u.by + 0.5f;
 
-    const TileRange rg = tile_range(offsets, lin, n_lin, n_isects);
-    float T[PPT], acc[PPT][GSB_CH];
+    const TileRange rg = tile_range(offsets, u.lin, n_lin, n_isects);
+    // alive[j] doubles as the alpha threshold: 1/255 while the pixel accumulates, +inf once it has
+    // stopped (or lies outside the image), so "alive && alpha >= 1/255" is ONE compare
+    float T[PPT], acc[PPT][GSB_CH], alive[PPT];
     int cur[PPT], stop_at[PPT];
-    unsigned live = 0;      // bit j: slot j still accumulating
+    unsigned inside = 0;
+    const float DEAD = __int_as_float(0x7f800000);
 #pragma unroll
     for (int j = 0; j < PPT; ++j) {
-        T[j] = 1.0f; cur[j] = 0; stop_at[j] = -1;
+        T[j] = 1.0f; cur[j] = 0; stop_at[j] = -1; alive[j] = DEAD;
 #pragma unroll
         for (int k = 0; k < GSB_CH; ++k) acc[j][k] = 0.f;
-        if (bx + (j & 1) * 8 < width && by + (j >> 1) * 4 < height) live |= 1u << j;
+        if (u.bx + SLOT_DX(j) < width && u.by + SLOT_DY(j) < height) { inside |= 1u << j; alive[j] = ALPHA_MIN; }
     }
-    const unsigned inside = live;
+    auto all_dead = [&]() -> bool {
+        bool d = true;
+#pragma unroll
+        for (int j = 0; j < PPT; ++j) d = d && alive[j] == DEAD;
+        return __all_sync(full, d);
+    };
 
     const int n = rg.end - rg.start;
     const int n_rounds = (n + RND - 1) / RND;
@@ -66,7 +66,7 @@ composite_fwd_kernel(const float4* __restrict__ rec, const int32_t* __restrict__
         issue_round(ws, 1, lane, rec, id1);
         int stage = 0;          // ring slot of round r
         for (int r = 0; r < n_rounds; ++r) {
-            if (__all_sync(full, live == 0)) break;
+            if (all_dead()) break;
             int st2 = stage + 2; if (st2 >= NSTAGE) st2 -= NSTAGE;
             s_ids[warp][st2][lane] = id_next;
             issue_round(ws, st2, lane, rec, id_next);
@@ -79,7 +79,7 @@ composite_fwd_kernel(const float4* __restrict__ rec, const int32_t* __restrict__
             {
                 const float4* raw = &ws.raw[stage][lane * 3];
                 float4 o0, o1, o2;
-                const bool keep = (li < rg.end) && stage_and_cull(raw[0], raw[1], raw[2], rc, li, o0, o1, o2);
+                const bool keep = (li < rg.end) && stage_and_cull(raw[0], raw[1], raw[2], u.rc, li, o0, o1, o2);
                 const unsigned m = __ballot_sync(full, keep);
                 n_keep = __popc(m);
                 if (keep) {
@@ -92,28 +92,21 @@ composite_fwd_kernel(const float4* __restrict__ rec, const int32_t* __restrict__
             // ---- composite the kept entries ----------------------------------------------------
             int cnt_reg = 0;    // lane k: pixels that counted kept entry k as "touched"
             for (int k = 0; k < n_keep; ++k) {
-                if ((k & 7) == 7 && __all_sync(full, live == 0)) break;
+                if ((k & 7) == 7 && all_dead()) break;
                 const float4 g0 = ws.k0[k];        // x, y, a', b'
                 const float4 g1 = ws.k1[k];        // c', list index, opacity, r
-                const float dx0 = g0.x - pxf, dx1 = dx0 - 8.0f;
-                const float dy0 = g0.y - pyf, dy1 = dy0 - 4.0f;
-                const float ax0 = g0.z * dx0, ax1 = g0.z * dx1;
-                const float cy0 = g1.x * dy0 * dy0, cy1 = g1.x * dy1 * dy1;
-                float sigma[PPT], alpha[PPT];
-                sigma[0] = fmaf(dx0, fmaf(g0.w, dy0, ax0), cy0);
-                sigma[1] = fmaf(dx1, fmaf(g0.w, dy0, ax1), cy0);
-                sigma[2] = fmaf(dx0, fmaf(g0.w, dy1, ax0), cy1);
-                sigma[3] = fmaf(dx1, fmaf(g0.w, dy1, ax1), cy1);
+                float dx[PPT], dy[PPT], sigma[PPT], alpha[PPT];
+                eval_sigma(g0, g1.x, pxf, pyf, dx, dy, sigma);
                 bool hit[PPT];
-                unsigned votes[PPT];
+                unsigned votes[PPT], any = 0;
 #pragma unroll
                 for (int j = 0; j < PPT; ++j) {
                     alpha[j] = fminf(ALPHA_MAX, g1.z * fast_ex2(-sigma[j]));
-                    hit[j] = ((live >> j) & 1u) && sigma[j] >= 0.f && alpha[j] >= ALPHA_MIN;
+                    hit[j] = alpha[j] >= alive[j] && sigma[j] >= 0.f;
                 }
 #pragma unroll
-                for (int j = 0; j < PPT; ++j) votes[j] = __ballot_sync(full, hit[j]);
-                if ((votes[0] | votes[1] | votes[2] | votes[3]) == 0u) continue;
+                for (int j = 0; j < PPT; ++j) { votes[j] = __ballot_sync(full, hit[j]); any |= votes[j]; }
+                if (any == 0u) continue;
                 const float4 g2 = ws.k2[k];        // g, b, depth, beta
                 const int idx = __float_as_int(g1.y);
                 int n_touch = 0;
@@ -134,10 +127,8 @@ composite_fwd_kernel(const float4* __restrict__ rec, const int32_t* __restrict__
                     if (COUNT) n_touch += __popc(__ballot_sync(full, take && T[j] > min_T));
                     cur[j] = take ? idx : cur[j];
                     T[j] = take ? next_T : T[j];
-                    if (stop) {
-                        live &= ~(1u << j);
-                        if (STATS) stop_at[j] = idx;
-                    }
+                    alive[j] = stop ? DEAD : alive[j];
+                    if (STATS && stop) stop_at[j] = idx;
                 }
                 if (COUNT && lane == k) cnt_reg = n_touch;
             }
@@ -150,14 +141,14 @@ composite_fwd_kernel(const float4* __restrict__ rec, const int32_t* __restrict__
     float bg[GSB_CH] = {0.f, 0.f, 0.f, 0.f, 0.f};
     if (backgrounds) {
 #pragma unroll
-        for (int k = 0; k < GSB_CH; ++k) bg[k] = backgrounds[cam * GSB_CH + k];
+        for (int k = 0; k < GSB_CH; ++k) bg[k] = backgrounds[u.cam * GSB_CH + k];
     }
     int visited = 0;
 #pragma unroll
     for (int j = 0; j < PPT; ++j) {
         if (!((inside >> j) & 1u)) continue;
-        const int x = bx + (j & 1) * 8, y = by + (j >> 1) * 4;
-        const size_t pix = ((size_t)cam * height + y) * width + x;
+        const int x = u.bx + SLOT_DX(j), y = u.by + SLOT_DY(j);
+        const size_t pix = ((size_t)u.cam * height + y) * width + x;
 #pragma unroll
         for (int k = 0; k < GSB_CH; ++k) render[pix * GSB_CH + k] = acc[j][k] + T[j] * bg[k];
         alphas[pix] = 1.0f - T[j];
@@ -184,9 +175,9 @@ GSB_API int gsb_composite_fwd(const float* rec, const int32_t* flatten_ids, cons
     GSB_CHECK_ARG(n_isects < ((int64_t)1 << 31));
     GSB_CHECK_ARG(tile_w == (width + GSB_TILE - 1) / GSB_TILE && tile_h == (height + GSB_TILE - 1) / GSB_TILE);
     const int64_t n_lin64 = (int64_t)C * tile_w * tile_h;
-    GSB_CHECK_ARG(n_lin64 * 2 < ((int64_t)1 << 31));
+    GSB_CHECK_ARG(n_lin64 * UNITS_PER_TILE < ((int64_t)1 << 31));
     const int n_lin = (int)n_lin64;
-    const int grid = (2 * n_lin + CMP_WARPS - 1) / CMP_WARPS;
+    const int grid = (UNITS_PER_TILE * n_lin + CMP_WARPS - 1) / CMP_WARPS;
     const float4* r4 = reinterpret_cast<const float4*>(rec);
     unsigned long long* pc = reinterpret_cast<unsigned long long*>(pair_count);
 #define GSB_FWD(COUNT, STATS)                                                                     \

@@ -1,17 +1,19 @@
 // Definitions shared by the compositing forward and backward kernels.
 //
-// Work decomposition (both directions): ONE WARP owns one 16x8 half-tile and walks the
-// tile's depth-sorted list on its own -- no CTA barrier anywhere.  Every thread owns FOUR
-// pixels: slot j of lane l is pixel (l & 7, l >> 3) of the j-th 8x4 block of the half-tile.
+// Work decomposition (both directions): ONE WARP (= one CTA) owns one 8x8 quarter-tile and
+// walks the tile's depth-sorted list on its own -- no CTA barrier anywhere.  Every thread owns
+// TWO pixels: slot j of lane l is pixel (l & 7, (l >> 3) + 4 j) of the quarter-tile.  Small units
+// keep ~8 of them per SM sub-partition (latency hiding, load balance: the hardware CTA scheduler
+// hands out the tail of the grid dynamically) and make the culling below sharper.
 //
 // The list is consumed in rounds of 32 entries.  Splat records (48 B) are gathered
 // from HBM/L2 into a three-stage shared-memory ring with cp.async (LDGSTS, 3 x 16 B per
 // lane), two rounds ahead of use; the ids that address them are prefetched one round
 // earlier still.  When a round lands, every lane takes one record, pre-scales the
 // conic by log2(e), and runs an EXACT ellipse-vs-rectangle test: the minimum of the
-// quadratic form over the half-tile's pixel-centre rectangle is compared with
+// quadratic form over the quarter-tile's pixel-centre rectangle is compared with
 // log2(255 * opacity), the largest exponent that can still reach alpha >= 1/255.
-// Entries that cannot touch the half-tile (about half of gsplat's 3-sigma bounding-
+// Entries that cannot touch the quarter-tile (about 60 % of gsplat's 3-sigma bounding-
 // square list) are dropped by a ballot/popc compaction, so the per-pixel loop only
 // sees splats that matter.
 #pragma once
@@ -22,11 +24,23 @@
 #define T_STOP 1e-4f
 #define LOG2E 1.4426950408889634f
 
-#define CMP_WARPS 2            // independent half-tile workers per CTA
+#define CMP_WARPS 1            // independent quarter-tile workers per CTA
 #define CMP_THREADS (32 * CMP_WARPS)
 #define RND 32                 // list entries per round (one per lane)
 #define NSTAGE 3               // cp.async ring depth
-#define PPT 4                  // pixels per thread
+#define PPT 2                  // pixels per thread: 2 -> 8x8 quarter-tile units, 4 -> 16x8 half-tiles
+#if PPT == 2
+#define UNITS_PER_TILE 4
+#define UNIT_W 8
+#define SLOT_DX(j) 0
+#define SLOT_DY(j) ((j) * 4)
+#else
+#define UNITS_PER_TILE 2
+#define UNIT_W 16
+#define SLOT_DX(j) (((j) & 1) * 8)
+#define SLOT_DY(j) (((j) >> 1) * 4)
+#endif
+#define UNIT_H 8
 
 struct TileRange {
     int start, end;
@@ -60,7 +74,7 @@ struct __align__(16) WarpStage {
     int32_t gid[RND];              //               flatten id (camera * N + gaussian)
 };
 
-// The half-tile's pixel-centre rectangle.
+// The quarter-tile's pixel-centre rectangle.
 struct Rect {
     float x0, x1, y0, y1;
 };
@@ -97,6 +111,41 @@ __device__ __forceinline__ bool stage_and_cull(const float4 r0, const float4 r1,
     const float dxm = fmaxf(fabsf(dxl), fabsf(dxh)), dym = fmaxf(fabsf(dyl), fabsf(dyh));
     const float margin = 1e-3f + 4e-6f * (A * dxm * dxm + fabsf(B) * dxm * dym + Cc * dym * dym);
     return q <= __log2f(255.0f * op) + margin;
+}
+
+// Which pixels a warp owns.
+struct Unit {
+    int lin, cam;        // camera * T + tile, camera
+    int bx, by;          // pixel of slot 0 of this lane
+    Rect rc;
+};
+
+__device__ __forceinline__ Unit decode_unit(int unit, int lane, int tile_w, int n_tiles) {
+    Unit u;
+    u.lin = unit / UNITS_PER_TILE;
+    const int q = unit - u.lin * UNITS_PER_TILE;
+    u.cam = u.lin / n_tiles;
+    const int tile = u.lin - u.cam * n_tiles;
+    const int ty = tile / tile_w, tx = tile - ty * tile_w;
+    const int ox = tx * GSB_TILE + (UNITS_PER_TILE == 4 ? (q & 1) * 8 : 0);
+    const int oy = ty * GSB_TILE + (UNITS_PER_TILE == 4 ? (q >> 1) * 8 : q * 8);
+    u.bx = ox + (lane & 7);
+    u.by = oy + (lane >> 3);
+    u.rc.x0 = (float)ox + 0.5f; u.rc.x1 = u.rc.x0 + (float)(UNIT_W - 1);
+    u.rc.y0 = (float)oy + 0.5f; u.rc.y1 = u.rc.y0 + (float)(UNIT_H - 1);
+    return u;
+}
+
+// sigma' of this lane's PPT pixels for the staged splat (x, y, a', b') / c'.
+__device__ __forceinline__ void eval_sigma(const float4 g0, float cc, float pxf, float pyf,
+                                           float (&dx)[PPT], float (&dy)[PPT], float (&sigma)[PPT]) {
+    const float dx0 = g0.x - pxf, dy0 = g0.y - pyf;
+#pragma unroll
+    for (int j = 0; j < PPT; ++j) {
+        dx[j] = dx0 - (float)SLOT_DX(j);
+        dy[j] = dy0 - (float)SLOT_DY(j);
+        sigma[j] = fmaf(dx[j], fmaf(g0.w, dy[j], g0.z * dx[j]), cc * dy[j] * dy[j]);
+    }
 }
 
 // Issue the gather of one round: lane copies the 48-byte record `id` into raw[stage][lane*3..].

@@ -6,16 +6,16 @@
 // each splat is a running suffix sum.
 //
 // Same decomposition as the forward kernel (composite.cuh): one independent warp per
-// 16x8 half-tile, FOUR pixels per thread, cp.async-staged rounds of 32 entries that are
-// culled against the half-tile and compacted before the per-pixel loop.  Consequences:
-//   * a thread sums the gradients of its 4 pixels in registers before any
-//     cross-lane traffic, so the warp reduction runs once per 128 pixels;
+// 8x8 quarter-tile, TWO pixels per thread, cp.async-staged rounds of 32 entries that are
+// culled against the unit and compacted before the per-pixel loop.  Consequences:
+//   * a thread sums the gradients of its pixels in registers before any
+//     cross-lane traffic, so the warp reduction runs once per 64 pixels;
 //   * a slot is a compact 8x4 block, so small splats leave whole slots without a
 //     hit and the warp skips their gradient math after one vote;
 //   * the reduction is a transposing butterfly: 16 values over 32 lanes in
 //     8+4+2+1+1 = 16 shuffles (a plain butterfly needs 11 x 5 = 55), after which
 //     16 lanes each hold one finished sum and park it in the warp's shared-memory row;
-//   * per (half-tile, kept Gaussian) one lane issues three float4 atomics to v_rec,
+//   * per (unit, kept Gaussian) one lane issues three float4 atomics to v_rec,
 //     32 Gaussians at a time.
 #include "composite.cuh"
 
@@ -52,7 +52,7 @@ __device__ __forceinline__ float transpose_reduce16(const float (&v)[16], int la
     return d;
 }
 
-__global__ void __maxnreg__(112)
+__global__ void __launch_bounds__(CMP_THREADS)
 composite_bwd_kernel(const float4* __restrict__ rec, const int32_t* __restrict__ flatten_ids,
                      const int32_t* __restrict__ offsets, const float* __restrict__ backgrounds,
                      int n_lin, int width, int height, int tile_w, int tile_h, int64_t n_isects,
@@ -64,42 +64,33 @@ composite_bwd_kernel(const float4* __restrict__ rec, const int32_t* __restrict__
     __shared__ __align__(16) float s_acc[CMP_WARPS][RND][12];
     const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int half_id = blockIdx.x * CMP_WARPS + warp;
-    const int lin = half_id >> 1, half = half_id & 1;
-    if (lin >= n_lin) return;
+    const int unit = blockIdx.x * CMP_WARPS + warp;
+    if (unit >= n_lin * UNITS_PER_TILE) return;
+    const Unit u = decode_unit(unit, lane, tile_w, tile_w * tile_h);
     WarpStage& ws = s_ws[warp];
     float (*acc_rows)[12] = s_acc[warp];
-    const int n_tiles = tile_w * tile_h;
-    const int cam = lin / n_tiles, tile = lin - cam * n_tiles;
-    const int ty = tile / tile_w, tx = tile - ty * tile_w;
-    // slot j -> pixel (bx + (j & 1) * 8, by + (j >> 1) * 4)
-    const int bx = tx * GSB_TILE + (lane & 7);
-    const int by = ty * GSB_TILE + half * 8 + (lane >> 3);
-    const float pxf = (float)bx + 0.5f, pyf = (float)by + 0.5f;
-    Rect rc;
-    rc.x0 = (float)(tx * GSB_TILE) + 0.5f; rc.x1 = rc.x0 + 15.0f;
-    rc.y0 = (float)(ty * GSB_TILE + half * 8) + 0.5f; rc.y1 = rc.y0 + 7.0f;
+    const float pxf = (float)u.bx + 0.5f, pyf = (float)u.by + 0.5f;
 
-    const TileRange rg = tile_range(offsets, lin, n_lin, n_isects);
+    const TileRange rg = tile_range(offsets, u.lin, n_lin, n_isects);
 
     float T[PPT], tail[PPT], vr[PPT][GSB_CH], buf[PPT][GSB_CH];
     int bin_final[PPT];
     float bgv[GSB_CH] = {0.f, 0.f, 0.f, 0.f, 0.f};
     if (backgrounds) {
 #pragma unroll
-        for (int k = 0; k < GSB_CH; ++k) bgv[k] = backgrounds[cam * GSB_CH + k];
+        for (int k = 0; k < GSB_CH; ++k) bgv[k] = backgrounds[u.cam * GSB_CH + k];
     }
     float vbg[GSB_CH] = {0.f, 0.f, 0.f, 0.f, 0.f};
     int my_last = -1;
 #pragma unroll
     for (int j = 0; j < PPT; ++j) {
-        const int x = bx + (j & 1) * 8, y = by + (j >> 1) * 4;
+        const int x = u.bx + SLOT_DX(j), y = u.by + SLOT_DY(j);
         const bool inside = x < width && y < height;
         T[j] = 1.f; tail[j] = 0.f; bin_final[j] = -1;
 #pragma unroll
         for (int k = 0; k < GSB_CH; ++k) { vr[j][k] = 0.f; buf[j][k] = 0.f; }
         if (inside) {
-            const size_t pix = ((size_t)cam * height + y) * width + x;
+            const size_t pix = ((size_t)u.cam * height + y) * width + x;
             const float T_final = 1.0f - render_alphas[pix];
             T[j] = T_final;
             bin_final[j] = last_ids[pix];
@@ -122,7 +113,7 @@ composite_bwd_kernel(const float4* __restrict__ rec, const int32_t* __restrict__
 #pragma unroll
         for (int k = 0; k < GSB_CH; ++k) {
             float s = warp_sum(vbg[k]);
-            if (lane == 0 && s != 0.f) atomicAdd(v_backgrounds + cam * GSB_CH + k, s);
+            if (lane == 0 && s != 0.f) atomicAdd(v_backgrounds + u.cam * GSB_CH + k, s);
         }
     }
     const int warp_last = __reduce_max_sync(full, my_last);
@@ -154,7 +145,7 @@ composite_bwd_kernel(const float4* __restrict__ rec, const int32_t* __restrict__
         {
             const float4* raw = &ws.raw[stage][lane * 3];
             float4 o0, o1, o2;
-            const bool keep = (li < range_end) && stage_and_cull(raw[0], raw[1], raw[2], rc, li, o0, o1, o2);
+            const bool keep = (li < range_end) && stage_and_cull(raw[0], raw[1], raw[2], u.rc, li, o0, o1, o2);
             const unsigned m = __ballot_sync(full, keep);
             n_keep = __popc(m);
             if (keep) {
@@ -169,18 +160,11 @@ composite_bwd_kernel(const float4* __restrict__ rec, const int32_t* __restrict__
             const float4 g0 = ws.k0[k];        // x, y, a', b'
             const float4 g1 = ws.k1[k];        // c', list index, opacity, r
             const int idx = __float_as_int(g1.y);
-            // Phase 1, branch-free: sigma', exp and alpha of the four pixels (chains overlap)
-            const float dx0 = g0.x - pxf, dx1 = dx0 - 8.0f;
-            const float dy0 = g0.y - pyf, dy1 = dy0 - 4.0f;
-            const float ax0 = g0.z * dx0, ax1 = g0.z * dx1;
-            const float cy0 = g1.x * dy0 * dy0, cy1 = g1.x * dy1 * dy1;
-            float sigma[PPT], vis[PPT], alpha[PPT];
-            sigma[0] = fmaf(dx0, fmaf(g0.w, dy0, ax0), cy0);
-            sigma[1] = fmaf(dx1, fmaf(g0.w, dy0, ax1), cy0);
-            sigma[2] = fmaf(dx0, fmaf(g0.w, dy1, ax0), cy1);
-            sigma[3] = fmaf(dx1, fmaf(g0.w, dy1, ax1), cy1);
+            // Phase 1, branch-free: sigma', exp and alpha of the lane's pixels (chains overlap)
+            float dx[PPT], dy[PPT], sigma[PPT], vis[PPT], alpha[PPT];
+            eval_sigma(g0, g1.x, pxf, pyf, dx, dy, sigma);
             bool valid[PPT];
-            unsigned votes[PPT];
+            unsigned votes[PPT], any = 0;
 #pragma unroll
             for (int j = 0; j < PPT; ++j) {
                 vis[j] = fast_ex2(-sigma[j]);
@@ -188,8 +172,8 @@ composite_bwd_kernel(const float4* __restrict__ rec, const int32_t* __restrict__
                 valid[j] = idx <= bin_final[j] && sigma[j] >= 0.f && alpha[j] >= ALPHA_MIN;
             }
 #pragma unroll
-            for (int j = 0; j < PPT; ++j) votes[j] = __ballot_sync(full, valid[j]);
-            if ((votes[0] | votes[1] | votes[2] | votes[3]) == 0u) continue;
+            for (int j = 0; j < PPT; ++j) { votes[j] = __ballot_sync(full, valid[j]); any |= votes[j]; }
+            if (any == 0u) continue;
             const float4 g2 = ws.k2[k];        // g, b, depth, beta
             const float col[GSB_CH] = {g1.w, g2.x, g2.y, g2.z, g2.w};
             float g[16];
@@ -199,7 +183,6 @@ composite_bwd_kernel(const float4* __restrict__ rec, const int32_t* __restrict__
 #pragma unroll
             for (int j = 0; j < PPT; ++j) {
                 if (votes[j] == 0u) continue;
-                const float dx = (j & 1) ? dx1 : dx0, dy = (j >> 1) ? dy1 : dy0;
                 const float al = valid[j] ? alpha[j] : 0.f;
                 const float ra = fast_rcp(1.0f - al);
                 const float Tn = T[j] * ra;
@@ -217,12 +200,12 @@ composite_bwd_kernel(const float4* __restrict__ rec, const int32_t* __restrict__
                 const float v_op = (valid[j] && ov <= ALPHA_MAX) ? vis[j] * v_alpha : 0.f;
                 const float vsp = v_sigma * (1.0f / LOG2E);
                 // d sigma'/d(x,y) with sigma' = a'dx^2 + b'dxdy + c'dy^2
-                g[0] = fmaf(vsp, 2.f * g0.z * dx + g0.w * dy, g[0]);
-                g[1] = fmaf(vsp, g0.w * dx + 2.f * g1.x * dy, g[1]);
+                g[0] = fmaf(vsp, 2.f * g0.z * dx[j] + g0.w * dy[j], g[0]);
+                g[1] = fmaf(vsp, g0.w * dx[j] + 2.f * g1.x * dy[j], g[1]);
                 g[2] += v_op;
-                g[3] = fmaf(0.5f * v_sigma * dx, dx, g[3]);
-                g[4] = fmaf(v_sigma * dx, dy, g[4]);
-                g[5] = fmaf(0.5f * v_sigma * dy, dy, g[5]);
+                g[3] = fmaf(0.5f * v_sigma * dx[j], dx[j], g[3]);
+                g[4] = fmaf(v_sigma * dx[j], dy[j], g[4]);
+                g[5] = fmaf(0.5f * v_sigma * dy[j], dy[j], g[5]);
             }
             int slot;
             const float total = transpose_reduce16(g, lane, slot);
@@ -256,9 +239,9 @@ GSB_API int gsb_composite_bwd(const float* rec, const int32_t* flatten_ids, cons
     GSB_CHECK_ARG(n_isects < ((int64_t)1 << 31));
     GSB_CHECK_ARG(tile_w == (width + GSB_TILE - 1) / GSB_TILE && tile_h == (height + GSB_TILE - 1) / GSB_TILE);
     const int64_t n_lin64 = (int64_t)C * tile_w * tile_h;
-    GSB_CHECK_ARG(n_lin64 * 2 < ((int64_t)1 << 31));
+    GSB_CHECK_ARG(n_lin64 * UNITS_PER_TILE < ((int64_t)1 << 31));
     const int n_lin = (int)n_lin64;
-    const int grid = (2 * n_lin + CMP_WARPS - 1) / CMP_WARPS;
+    const int grid = (UNITS_PER_TILE * n_lin + CMP_WARPS - 1) / CMP_WARPS;
     composite_bwd_kernel<<<grid, CMP_THREADS, 0, gsb_stream(stream)>>>(
         reinterpret_cast<const float4*>(rec), flatten_ids, offsets, backgrounds, n_lin, width, height,
         tile_w, tile_h, n_isects, render_alphas, last_ids, v_render, v_alphas, v_rec, v_backgrounds);
