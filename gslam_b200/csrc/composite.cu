@@ -28,6 +28,7 @@ composite_fwd_kernel(const float4* __restrict__ rec, const int32_t* __restrict__
     if (unit >= n_lin * UNITS_PER_TILE) return;
     const Unit u = decode_unit(unit, lane, tile_w, tile_w * tile_h);
     WarpStage& ws = s_ws[warp];
+    const unsigned k_base = smem_addr(ws.k0);
     const float pxf = (float)u.bx + 0.5f, pyf = (float)u.by + 0.5f;
 
     const TileRange rg = tile_range(offsets, u.lin, n_lin, n_isects);
@@ -93,8 +94,9 @@ composite_fwd_kernel(const float4* __restrict__ rec, const int32_t* __restrict__
             int cnt_reg = 0;    // lane k: pixels that counted kept entry k as "touched"
             for (int k = 0; k < n_keep; ++k) {
                 if ((k & 7) == 7 && all_dead()) break;
-                const float4 g0 = ws.k0[k];        // x, y, a', b'
-                const float4 g1 = ws.k1[k];        // c', list index, opacity, r
+                const unsigned ka = k_base + (unsigned)k * 16u;
+                const float4 g0 = lds128(ka);                        // x, y, a', b'
+                const float4 g1 = lds128(ka + K_PLANE_BYTES);        // c', list index, opacity, r
                 float dx[PPT], dy[PPT], sigma[PPT], alpha[PPT];
                 eval_sigma(g0, g1.x, pxf, pyf, dx, dy, sigma);
                 bool hit[PPT];
@@ -107,7 +109,7 @@ composite_fwd_kernel(const float4* __restrict__ rec, const int32_t* __restrict__
 #pragma unroll
                 for (int j = 0; j < PPT; ++j) { votes[j] = __ballot_sync(full, hit[j]); any |= votes[j]; }
                 if (any == 0u) continue;
-                const float4 g2 = ws.k2[k];        // g, b, depth, beta
+                const float4 g2 = lds128(ka + 2 * K_PLANE_BYTES);    // g, b, depth, beta
                 const int idx = __float_as_int(g1.y);
                 int n_touch = 0;
 #pragma unroll

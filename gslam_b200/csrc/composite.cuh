@@ -65,6 +65,24 @@ __device__ __forceinline__ void cp_async_wait() {
     asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
 }
 
+// 16-byte shared-memory load from a 32-bit shared-window address (keeps the address arithmetic of the
+// hot loops to one add: the generic-pointer path re-derives the window base every iteration).
+__device__ __forceinline__ float4 lds128(unsigned addr) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr) : "memory");
+    return v;
+}
+#define K_PLANE_BYTES (RND * 16)   // k0, k1, k2 are contiguous in WarpStage
+
+// Shared-window address of p, pinned in a register (the opaque move stops the compiler from
+// re-deriving it from SR_CgaCtaId inside the hot loop).
+__device__ __forceinline__ unsigned smem_addr(const void* p) {
+    unsigned a = (unsigned)__cvta_generic_to_shared(p), r;
+    asm volatile("mov.u32 %0, %1;" : "=r"(r) : "r"(a));
+    return r;
+}
+
 // Per-warp staging area.
 struct __align__(16) WarpStage {
     float4 raw[NSTAGE][RND * 3];   // ring of gathered records, lane-major (48 B per lane)

@@ -12,44 +12,21 @@
 //     cross-lane traffic, so the warp reduction runs once per 64 pixels;
 //   * a slot is a compact 8x4 block, so small splats leave whole slots without a
 //     hit and the warp skips their gradient math after one vote;
-//   * the reduction is a transposing butterfly: 16 values over 32 lanes in
-//     8+4+2+1+1 = 16 shuffles (a plain butterfly needs 11 x 5 = 55), after which
-//     16 lanes each hold one finished sum and park it in the warp's shared-memory row;
+//   * the 11 sums of an entry cross the warp through shared memory: 11 conflict-free stores, four
+//     16-byte loads and 15 adds on lanes 2c+h, one shuffle (a shuffle butterfly costs 55, a
+//     transposing one 16 shuffles + 30 selects); the colour-behind state is ONE scalar per pixel
+//     (behind . v_render) instead of a 5-vector;
 //   * per (unit, kept Gaussian) one lane issues three float4 atomics to v_rec,
 //     32 Gaussians at a time.
 #include "composite.cuh"
 
-// Sum v[0..15] over the warp.  On return lane l holds in `out` the total of value
-// index idx(l) = 8*b4 + 4*b3 + 2*b2 + b1 (b_k = bit k of l); lanes l and l^1 agree.
-__device__ __forceinline__ float transpose_reduce16(const float (&v)[16], int lane, int& idx) {
-    const unsigned full = 0xffffffffu;
-    float a[8], b[4], c[2], d;
-    bool up = lane & 16;
-#pragma unroll
-    for (int k = 0; k < 8; ++k) {
-        float keep = up ? v[k + 8] : v[k], send = up ? v[k] : v[k + 8];
-        a[k] = keep + __shfl_xor_sync(full, send, 16);
-    }
-    up = lane & 8;
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-        float keep = up ? a[k + 4] : a[k], send = up ? a[k] : a[k + 4];
-        b[k] = keep + __shfl_xor_sync(full, send, 8);
-    }
-    up = lane & 4;
-#pragma unroll
-    for (int k = 0; k < 2; ++k) {
-        float keep = up ? b[k + 2] : b[k], send = up ? b[k] : b[k + 2];
-        c[k] = keep + __shfl_xor_sync(full, send, 4);
-    }
-    up = lane & 2;
-    {
-        float keep = up ? c[1] : c[0], send = up ? c[0] : c[1];
-        d = keep + __shfl_xor_sync(full, send, 2);
-    }
-    d += __shfl_xor_sync(full, d, 1);
-    idx = ((lane >> 4) & 1) * 8 + ((lane >> 3) & 1) * 4 + ((lane >> 2) & 1) * 2 + ((lane >> 1) & 1);
-    return d;
+#define GRAD_N 11                       // gradient sums per (unit, Gaussian)
+#define RED_STRIDE 36                   // floats per row of the reduction tile: 32 lanes + 4 pad, so the
+                                        // 16-byte row reads of lanes 2c+h fall in distinct bank groups
+#define RED_BYTES (GRAD_N * RED_STRIDE * 4)
+
+__device__ __forceinline__ void sts32(unsigned addr, float v) {
+    asm volatile("st.shared.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory");
 }
 
 __global__ void __launch_bounds__(CMP_THREADS)
@@ -62,6 +39,7 @@ composite_bwd_kernel(const float4* __restrict__ rec, const int32_t* __restrict__
     __shared__ WarpStage s_ws[CMP_WARPS];
     __shared__ int32_t s_ids[CMP_WARPS][NSTAGE][RND];
     __shared__ __align__(16) float s_acc[CMP_WARPS][RND][12];
+    __shared__ __align__(16) float s_red[CMP_WARPS][2][GRAD_N * RED_STRIDE];
     const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int unit = blockIdx.x * CMP_WARPS + warp;
@@ -69,11 +47,13 @@ composite_bwd_kernel(const float4* __restrict__ rec, const int32_t* __restrict__
     const Unit u = decode_unit(unit, lane, tile_w, tile_w * tile_h);
     WarpStage& ws = s_ws[warp];
     float (*acc_rows)[12] = s_acc[warp];
+    const unsigned k_base = smem_addr(ws.k0);
+    const unsigned red_base = smem_addr(s_red[warp]);
     const float pxf = (float)u.bx + 0.5f, pyf = (float)u.by + 0.5f;
 
     const TileRange rg = tile_range(offsets, u.lin, n_lin, n_isects);
 
-    float T[PPT], tail[PPT], vr[PPT][GSB_CH], buf[PPT][GSB_CH];
+    float T[PPT], tail[PPT], vr[PPT][GSB_CH], behind[PPT];
     int bin_final[PPT];
     float bgv[GSB_CH] = {0.f, 0.f, 0.f, 0.f, 0.f};
     if (backgrounds) {
@@ -88,7 +68,8 @@ composite_bwd_kernel(const float4* __restrict__ rec, const int32_t* __restrict__
         const bool inside = x < width && y < height;
         T[j] = 1.f; tail[j] = 0.f; bin_final[j] = -1;
 #pragma unroll
-        for (int k = 0; k < GSB_CH; ++k) { vr[j][k] = 0.f; buf[j][k] = 0.f; }
+        for (int k = 0; k < GSB_CH; ++k) vr[j][k] = 0.f;
+        behind[j] = 0.f;
         if (inside) {
             const size_t pix = ((size_t)u.cam * height + y) * width + x;
             const float T_final = 1.0f - render_alphas[pix];
@@ -156,9 +137,11 @@ composite_bwd_kernel(const float4* __restrict__ rec, const int32_t* __restrict__
         }
         __syncwarp();
         unsigned wrote = 0;      // bit k: kept entry k produced a gradient row
+        unsigned red_flip = 0;
         for (int k = n_keep - 1; k >= 0; --k) {
-            const float4 g0 = ws.k0[k];        // x, y, a', b'
-            const float4 g1 = ws.k1[k];        // c', list index, opacity, r
+            const unsigned ka = k_base + (unsigned)k * 16u;
+            const float4 g0 = lds128(ka);                        // x, y, a', b'
+            const float4 g1 = lds128(ka + K_PLANE_BYTES);        // c', list index, opacity, r
             const int idx = __float_as_int(g1.y);
             // Phase 1, branch-free: sigma', exp and alpha of the lane's pixels (chains overlap)
             float dx[PPT], dy[PPT], sigma[PPT], vis[PPT], alpha[PPT];
@@ -174,48 +157,73 @@ composite_bwd_kernel(const float4* __restrict__ rec, const int32_t* __restrict__
 #pragma unroll
             for (int j = 0; j < PPT; ++j) { votes[j] = __ballot_sync(full, valid[j]); any |= votes[j]; }
             if (any == 0u) continue;
-            const float4 g2 = ws.k2[k];        // g, b, depth, beta
+            const float4 g2 = lds128(ka + 2 * K_PLANE_BYTES);    // g, b, depth, beta
             const float col[GSB_CH] = {g1.w, g2.x, g2.y, g2.z, g2.w};
-            float g[16];
+            // raw sums of this lane: [0] sum w_x  [1] sum w_y  [2] v_opacity  [3] sum w_x dx
+            // [4] sum w_x dy  [5] sum w_y dy  [6..10] v_colour, with w_x = v_sigma dx, w_y = v_sigma dy;
+            // the conic-dependent finish (v_x, v_y, the halves) happens once per entry at the flush
+            float g[GRAD_N];
 #pragma unroll
-            for (int q = 0; q < 16; ++q) g[q] = 0.f;
+            for (int q = 0; q < GRAD_N; ++q) g[q] = 0.f;
             // Phase 2: per 8x4 block, a warp-uniform branch; inside, misses are predicated (alpha = 0)
 #pragma unroll
             for (int j = 0; j < PPT; ++j) {
                 if (votes[j] == 0u) continue;
                 const float al = valid[j] ? alpha[j] : 0.f;
                 const float ra = fast_rcp(1.0f - al);
-                const float Tn = T[j] * ra;
+                const float Tn = T[j] * ra;          // transmittance in front of this splat
                 const float fac = al * Tn;
-                float v_alpha = tail[j] * ra;
+                float E = col[0] * vr[j][0];         // <colour, v_render>
 #pragma unroll
-                for (int q = 0; q < GSB_CH; ++q) {
-                    g[6 + q] = fmaf(fac, vr[j][q], g[6 + q]);
-                    v_alpha = fmaf(fmaf(col[q], Tn, -buf[j][q] * ra), vr[j][q], v_alpha);
-                    buf[j][q] = fmaf(col[q], fac, buf[j][q]);
-                }
+                for (int q = 1; q < GSB_CH; ++q) E = fmaf(col[q], vr[j][q], E);
+#pragma unroll
+                for (int q = 0; q < GSB_CH; ++q) g[6 + q] = fmaf(fac, vr[j][q], g[6 + q]);
+                // dL/dalpha = T E - (behind . v_render + T_final (bg . v_render - v_alpha)) / (1 - alpha)
+                const float v_alpha = fmaf(Tn, E, ra * (tail[j] - behind[j]));
+                behind[j] = fmaf(fac, E, behind[j]);
                 T[j] = Tn;
                 const float ov = g1.z * vis[j];
-                const float v_sigma = (valid[j] && ov <= ALPHA_MAX) ? -ov * v_alpha : 0.f;
-                const float v_op = (valid[j] && ov <= ALPHA_MAX) ? vis[j] * v_alpha : 0.f;
-                const float vsp = v_sigma * (1.0f / LOG2E);
-                // d sigma'/d(x,y) with sigma' = a'dx^2 + b'dxdy + c'dy^2
-                g[0] = fmaf(vsp, 2.f * g0.z * dx[j] + g0.w * dy[j], g[0]);
-                g[1] = fmaf(vsp, g0.w * dx[j] + 2.f * g1.x * dy[j], g[1]);
-                g[2] += v_op;
-                g[3] = fmaf(0.5f * v_sigma * dx[j], dx[j], g[3]);
-                g[4] = fmaf(v_sigma * dx[j], dy[j], g[4]);
-                g[5] = fmaf(0.5f * v_sigma * dy[j], dy[j], g[5]);
+                const bool live = valid[j] && ov <= ALPHA_MAX;
+                const float v_sigma = live ? -ov * v_alpha : 0.f;
+                g[2] += live ? vis[j] * v_alpha : 0.f;
+                const float wx = v_sigma * dx[j], wy = v_sigma * dy[j];
+                g[0] += wx;
+                g[1] += wy;
+                g[3] = fmaf(wx, dx[j], g[3]);
+                g[4] = fmaf(wx, dy[j], g[4]);
+                g[5] = fmaf(wy, dy[j], g[5]);
             }
-            int slot;
-            const float total = transpose_reduce16(g, lane, slot);
-            if (!(lane & 1) && slot < 12) acc_rows[k][slot] = total;     // slot 11 is always 0
+            // ---- warp reduction through shared memory: 11 conflict-free stores, then lane 2c+h sums
+            // half a row with four 16-byte loads; one shuffle joins the halves
+            const unsigned rb = red_base + red_flip;
+            red_flip ^= RED_BYTES;      // double buffer: the next entry's stores cannot race these loads
+#pragma unroll
+            for (int q = 0; q < GRAD_N; ++q) sts32(rb + (unsigned)(q * RED_STRIDE * 4) + lane * 4u, g[q]);
+            __syncwarp();
+            float total = 0.f;
+            if (lane < 2 * GRAD_N) {
+                const unsigned ra4 = rb + (unsigned)((lane >> 1) * RED_STRIDE * 4 + (lane & 1) * 64);
+                const float4 v0 = lds128(ra4), v1 = lds128(ra4 + 16), v2 = lds128(ra4 + 32), v3 = lds128(ra4 + 48);
+                total = (((v0.x + v0.y) + (v0.z + v0.w)) + ((v1.x + v1.y) + (v1.z + v1.w))) +
+                        (((v2.x + v2.y) + (v2.z + v2.w)) + ((v3.x + v3.y) + (v3.z + v3.w)));
+            }
+            total += __shfl_xor_sync(full, total, 1);
+            if (lane < 2 * GRAD_N && !(lane & 1)) acc_rows[k][lane >> 1] = total;
             wrote |= 1u << k;
         }
         __syncwarp();
         if ((wrote >> lane) & 1u) {
             const float4* a = reinterpret_cast<const float4*>(&acc_rows[lane][0]);
-            const float4 a0 = a[0], a1 = a[1], a2 = a[2];
+            float4 a0 = a[0], a1 = a[1], a2 = a[2];
+            // finish with this entry's conic: d sigma'/d(x,y) = (2a'dx + b'dy, b'dx + 2c'dy), sigma' = sigma log2(e)
+            const float4 c0 = ws.k0[lane];
+            const float cc = ws.k1[lane].x;
+            const float sx = a0.x * (1.0f / LOG2E), sy = a0.y * (1.0f / LOG2E);
+            a0.x = 2.f * c0.z * sx + c0.w * sy;
+            a0.y = c0.w * sx + 2.f * cc * sy;
+            a0.w *= 0.5f;            // d sigma / d conic_a = dx^2 / 2
+            a1.y *= 0.5f;            // d sigma / d conic_c = dy^2 / 2
+            a2.w = 0.f;
             float4* dst = reinterpret_cast<float4*>(v_rec) + (size_t)ws.gid[lane] * 3;
             atomicAdd(dst, a0);
             atomicAdd(dst + 1, a1);
