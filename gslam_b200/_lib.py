@@ -13,7 +13,8 @@ from typing import Optional
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libgsb.so")
+# GSB_LIB overrides the path (kernel A/B experiments); the default is the in-tree build
+LIB_PATH = os.environ.get("GSB_LIB") or os.path.join(_HERE, "libgsb.so")
 HEADER_PATH = os.path.join(os.path.dirname(_HERE), "include", "gsb.h")
 
 _p = ct.c_void_p
