@@ -42,6 +42,8 @@ def parse():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--n-gauss", type=int, default=N_GAUSS)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--map-gauss", type=int, default=500_000)
+    ap.add_argument("--no-mapping", action="store_true")
     return ap.parse_args()
 
 
@@ -155,6 +157,57 @@ class ClockSampler:
         os.unlink(self.f.name)
         return {"sm_mhz": statistics.median(sm) if sm else None,
                 "sm_max_mhz": max(mx) if mx else None, "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def mapping_leg(args, dev, rank, world):
+    """Second half of BASELINE.json's metric: mapping views/s (configs[2] shape: 8-keyframe window,
+    500k Gaussians, render + photometric/SSIM losses + backward + gradient all-reduce + Adam +
+    opacity decay = the body of Backend.optimize_map, gslam/backend.py:260-359), the window's
+    views sharded window[rank::world] (strong scaling: the window is fixed at 8 views)."""
+    import torch
+    import torch.distributed as dist
+    from gslam_b200.mapping import DEFAULT_LRS, PARAM_NAMES, FlatSplats, MappingStep, shard_views
+    from gslam_b200.optim import FusedAdam
+    from gslam_b200.synthetic import make_scene, target_images
+
+    n_views, n = 8, args.map_gauss
+    sc = make_scene(n, n_views, "tum", 1.0)
+    mine = shard_views(n_views, rank, world)
+    if not mine:
+        mine = [rank % n_views]          # more ranks than views: replicate (never at 1/2/4/8)
+    g = sc.to(dev)
+    splats = FlatSplats(g.params())
+    opt = FusedAdam([dict(params=[p], lr=DEFAULT_LRS[nm]) for p, nm in zip(splats.params, PARAM_NAMES)])
+    step = MappingStep(splats, opt)
+    vm, K = g.viewmats[mine].contiguous(), g.Ks[mine].contiguous()
+    gt = target_images(n_views, sc.height, sc.width)[mine].to(dev)
+    exposure = torch.zeros(len(mine), 2, device=dev)
+    steps = max(3, min(args.steps, 20))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(3):
+        step(vm, K, gt, exposure, sc.width, sc.height, n_views)
+    barrier()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+    for e0, e1 in ev:
+        e0.record()
+        step(vm, K, gt, exposure, sc.width, sc.height, n_views)
+        e1.record()
+    barrier()
+    ms = sum(a.elapsed_time(b) for a, b in ev) / steps
+    t = torch.tensor([ms], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    return {"metric": "mapping views/s (8-keyframe window, full optimize_map step)", "value": n_views * 1e3 / ms,
+            "unit": "views/s", "ms_per_step": ms, "steps": steps, "n_views": n_views, "n_gauss": n,
+            "views_per_rank": len(mine), "scaling": "strong",
+            "step": "render RGB+D+beta, exposure + active-NeRF NLL + 0.2 SSIM(valid), backward, "
+                    "flat-gradient all-reduce, isotropic reg, fused Adam + opacity decay (eager launches)"}
 
 
 def run_ours(args):
@@ -313,6 +366,10 @@ def run_ours(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     e2e_value = world * 1e3 / float(t.item())
 
+    mapping = None
+    if not args.no_mapping:
+        mapping = mapping_leg(args, dev, rank, world)
+
     if rank == 0:
         hbm, which, sm_max = peaks()
         CN, px = n, H * W
@@ -375,6 +432,7 @@ def run_ours(args):
             "clocks": clocks,
             "roofline": roofline,
             "roofline_stages": stages,
+            "mapping": mapping,
         }
         if world == 1 and not args.no_cpu_baseline:
             v, tsec, cores, sample = cpu_oracle_rate(n, band_rows=30, reps=1)
