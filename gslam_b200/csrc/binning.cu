@@ -133,11 +133,8 @@ GSB_API int gsb_isect_scatter(const float* means2d, const int32_t* radii, const 
 // memory.  O(L) work instead of the O(L log^2 L) of a pure bitonic sort.
 // ---------------------------------------------------------------------------
 #define SEG_THREADS 256
-#define SEG_SMEM_ELEMS 2048      // keys staged in shared memory (2 x 16 KB)
-#define SEG_MAX_BUCKETS 4096     // counters: 2 x 16 KB when the key staging area is not used
 #define SEG_SMALL 24             // buckets up to this size are insertion-sorted by one thread
 #define SEG_MAX_BIG 64
-#define SEG_SMEM_BYTES (2 * SEG_MAX_BUCKETS * 4 + 2 * SEG_SMEM_ELEMS * 8)
 
 // all compare-exchanges ascending, so a non-power-of-two length needs no padding
 // (out-of-range partners act as +inf)
@@ -171,14 +168,14 @@ __device__ __forceinline__ void bitonic_sort(uint64_t* a, int L) {
 
 // Sorts in[0..L) into out[0..L).  cnt / fill: B ints each in shared memory.
 __device__ __forceinline__ void bucket_sort(const uint64_t* in, uint64_t* out, int L, int* cnt,
-                                            int* fill) {
+                                            int* fill, int max_buckets) {
     __shared__ uint32_t red_mn[SEG_THREADS / 32], red_mx[SEG_THREADS / 32];
     __shared__ int warp_sum_s[SEG_THREADS / 32];
     __shared__ int big[SEG_MAX_BIG];
     __shared__ int n_big;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     int lgB = 0;
-    while ((1 << lgB) < L && (1 << lgB) < SEG_MAX_BUCKETS) ++lgB;
+    while ((1 << lgB) < L && (1 << lgB) < max_buckets) ++lgB;
     const int B = 1 << lgB;
     // 1. depth range
     uint32_t mn = 0xffffffffu, mx = 0u;
@@ -261,15 +258,26 @@ __device__ __forceinline__ void bucket_sort(const uint64_t* in, uint64_t* out, i
     for (int k = 0; k < nb; ++k) bitonic_sort(out + cnt[big[k]], fill[big[k]]);
 }
 
+// Segments of up to KPT * 256 keys: the keys are read from global memory ONCE into registers
+// (KPT per thread), bucketed through one shared-memory counter array (histogram -> exclusive
+// scan -> the scanned counters double as scatter cursors, so afterwards cnt[b] is the END of
+// bucket b) and finished in a shared-memory output array.  Shared memory is 12 bytes per key,
+// so a 2048-key configuration keeps nine CTAs per SM resident.  Longer segments take the
+// generic path through global scratch.
+template <int KPT>
 __global__ void __launch_bounds__(SEG_THREADS)
 segment_sort_kernel(uint64_t* __restrict__ dk, uint64_t* __restrict__ tmp,
                     const int32_t* __restrict__ offsets, int n_tiles, int tile_n_bits, int64_t capacity,
                     int64_t* __restrict__ isect_ids, int32_t* __restrict__ flatten_ids) {
+    constexpr int ELEMS = KPT * SEG_THREADS;
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    int* cnt = reinterpret_cast<int*>(smem_raw);
-    int* fill = cnt + SEG_MAX_BUCKETS;
-    uint64_t* sa = reinterpret_cast<uint64_t*>(fill + SEG_MAX_BUCKETS);
-    uint64_t* sb = sa + SEG_SMEM_ELEMS;
+    uint64_t* out = reinterpret_cast<uint64_t*>(smem_raw);            // ELEMS keys
+    int* cnt = reinterpret_cast<int*>(out + ELEMS);                   // ELEMS counters
+    __shared__ uint32_t red_mn[SEG_THREADS / 32], red_mx[SEG_THREADS / 32];
+    __shared__ int warp_sum_s[SEG_THREADS / 32];
+    __shared__ int big[SEG_MAX_BIG];
+    __shared__ int n_big;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int lin = blockIdx.x;                 // camera * n_tiles + tile
     int64_t s = offsets[lin], e = offsets[lin + 1];
     if (e > capacity) e = capacity;
@@ -278,16 +286,99 @@ segment_sort_kernel(uint64_t* __restrict__ dk, uint64_t* __restrict__ tmp,
     const int cam = lin / n_tiles, tile = lin % n_tiles;
     const int64_t hi = (((int64_t)cam << tile_n_bits) | tile) << 32;
     const uint64_t* sorted;
-    if (L == 1) {
-        sorted = dk + s;
-    } else if (L <= SEG_SMEM_ELEMS) {
-        for (int t = threadIdx.x; t < L; t += SEG_THREADS) sa[t] = dk[s + t];
-        __syncthreads();
-        bucket_sort(sa, sb, L, cnt, fill);
-        sorted = sb;
-    } else {
-        bucket_sort(dk + s, tmp + s, L, cnt, fill);
+    if (L > ELEMS) {
+        // generic path: global in / out, counters in shared memory (fill aliases the key array)
+        bucket_sort(dk + s, tmp + s, L, cnt, reinterpret_cast<int*>(out), ELEMS);
         sorted = tmp + s;
+    } else if (L == 1) {
+        sorted = dk + s;
+    } else {
+        uint64_t key[KPT];
+        uint32_t mn = 0xffffffffu, mx = 0u;
+#pragma unroll
+        for (int i = 0; i < KPT; ++i) {
+            const int t = tid + i * SEG_THREADS;
+            key[i] = t < L ? dk[s + t] : ~0ull;
+            if (t < L) {
+                const uint32_t d = (uint32_t)(key[i] >> 32);
+                mn = min(mn, d); mx = max(mx, d);
+            }
+        }
+        int lgB = 0;
+        while ((1 << lgB) < L) ++lgB;           // L <= ELEMS, a power of two
+        const int B = 1 << lgB;
+        mn = __reduce_min_sync(0xffffffffu, mn);
+        mx = __reduce_max_sync(0xffffffffu, mx);
+        if (lane == 0) { red_mn[warp] = mn; red_mx[warp] = mx; }
+        for (int t = tid; t < B; t += SEG_THREADS) cnt[t] = 0;
+        if (tid == 0) n_big = 0;
+        __syncthreads();
+#pragma unroll
+        for (int w = 0; w < SEG_THREADS / 32; ++w) { mn = min(mn, red_mn[w]); mx = max(mx, red_mx[w]); }
+        // monotone map of the depth bits to B buckets (about one key per bucket)
+        const float scale = (float)B / ((float)(mx - mn) + 1.0f);
+        auto bucket_of = [&](uint64_t k) -> int {
+            return min(B - 1, (int)((float)((uint32_t)(k >> 32) - mn) * scale));
+        };
+#pragma unroll
+        for (int i = 0; i < KPT; ++i)
+            if (tid + i * SEG_THREADS < L) atomicAdd(&cnt[bucket_of(key[i])], 1);
+        __syncthreads();
+        {   // exclusive scan of cnt, in place (B / 256 consecutive counters per thread)
+            const int per = max(B / SEG_THREADS, 1);
+            const int b0 = tid * per;
+            int local = 0;
+            if (b0 < B)
+                for (int k = 0; k < per; ++k) local += cnt[b0 + k];
+            int x = local;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                int y = __shfl_up_sync(0xffffffffu, x, o);
+                if (lane >= o) x += y;
+            }
+            if (lane == 31) warp_sum_s[warp] = x;
+            __syncthreads();
+            int base = 0;
+            for (int w = 0; w < warp; ++w) base += warp_sum_s[w];
+            int run = base + x - local;
+            if (b0 < B)
+                for (int k = 0; k < per; ++k) {
+                    int c = cnt[b0 + k];
+                    cnt[b0 + k] = run;
+                    run += c;
+                }
+        }
+        __syncthreads();
+#pragma unroll
+        for (int i = 0; i < KPT; ++i)
+            if (tid + i * SEG_THREADS < L) out[atomicAdd(&cnt[bucket_of(key[i])], 1)] = key[i];
+        __syncthreads();
+        // cnt[b] is now the end of bucket b; finish the buckets
+        for (int bkt = tid; bkt < B; bkt += SEG_THREADS) {
+            const int s0 = bkt ? cnt[bkt - 1] : 0, m = cnt[bkt] - s0;
+            if (m < 2) continue;
+            bool small = m <= SEG_SMALL;
+            if (!small) {
+                int slot = atomicAdd(&n_big, 1);
+                if (slot < SEG_MAX_BIG) big[slot] = bkt;
+                else small = true;          // list full: slow but correct
+            }
+            if (small) {
+                for (int i = 1; i < m; ++i) {
+                    uint64_t k = out[s0 + i];
+                    int j = i - 1;
+                    while (j >= 0 && out[s0 + j] > k) { out[s0 + j + 1] = out[s0 + j]; --j; }
+                    out[s0 + j + 1] = k;
+                }
+            }
+        }
+        __syncthreads();
+        const int nb = min(n_big, SEG_MAX_BIG);
+        for (int k = 0; k < nb; ++k) {
+            const int bkt = big[k], s0 = bkt ? cnt[bkt - 1] : 0;
+            bitonic_sort(out + s0, cnt[bkt] - s0);
+        }
+        sorted = out;
     }
     __syncthreads();
     for (int t = threadIdx.x; t < L; t += SEG_THREADS) {
@@ -297,23 +388,41 @@ segment_sort_kernel(uint64_t* __restrict__ dk, uint64_t* __restrict__ tmp,
     }
 }
 
+template <int KPT>
+static int launch_segment_sort(int n, uint64_t* dk, uint64_t* tmp, const int32_t* offsets, int n_tiles,
+                               int tile_n_bits, int64_t capacity, int64_t* isect_ids, int32_t* flatten_ids,
+                               cudaStream_t st) {
+    const int smem = KPT * SEG_THREADS * 12;
+    static bool attr_set[64] = {false};
+    int dev = 0;
+    GSB_CUDA(cudaGetDevice(&dev));
+    if (dev >= 64 || !attr_set[dev]) {   // the opt-in above 48 KB is a per-device attribute
+        GSB_CUDA(cudaFuncSetAttribute(segment_sort_kernel<KPT>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        if (dev < 64) attr_set[dev] = true;
+    }
+    segment_sort_kernel<KPT><<<n, SEG_THREADS, smem, st>>>(dk, tmp, offsets, n_tiles, tile_n_bits, capacity,
+                                                          isect_ids, flatten_ids);
+    GSB_LAUNCH_CHECK();
+    return 0;
+}
+
 GSB_API int gsb_segment_sort(int64_t* depth_id, int64_t* scratch, const int32_t* offsets, int C,
                              int tile_w, int tile_h, int tile_n_bits, int64_t capacity,
                              int64_t* isect_ids, int32_t* flatten_ids, void* stream) {
     int n = C * tile_w * tile_h;
     if (n == 0 || capacity == 0) return 0;
     GSB_CHECK_ARG(depth_id && scratch && offsets && isect_ids && flatten_ids);
-    static bool attr_set[64] = {false};
-    int dev = 0;
-    GSB_CUDA(cudaGetDevice(&dev));
-    if (dev >= 64 || !attr_set[dev]) {   // the opt-in above 48 KB is a per-device attribute
-        GSB_CUDA(cudaFuncSetAttribute(segment_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      SEG_SMEM_BYTES));
-        if (dev < 64) attr_set[dev] = true;
-    }
-    segment_sort_kernel<<<n, SEG_THREADS, SEG_SMEM_BYTES, gsb_stream(stream)>>>(
-        reinterpret_cast<uint64_t*>(depth_id), reinterpret_cast<uint64_t*>(scratch), offsets,
-        tile_w * tile_h, tile_n_bits, capacity, isect_ids, flatten_ids);
-    GSB_LAUNCH_CHECK();
-    return 0;
+    uint64_t* dk = reinterpret_cast<uint64_t*>(depth_id);
+    uint64_t* tmp = reinterpret_cast<uint64_t*>(scratch);
+    // the configuration follows the mean segment length (capacity bounds the intersection count):
+    // 2048-key CTAs (24 KB, nine per SM) while the mean leaves 1.5x headroom, else 4096 / 8192
+    const int64_t mean = capacity / n;
+    if (mean * 3 <= 2048 * 2)
+        return launch_segment_sort<8>(n, dk, tmp, offsets, tile_w * tile_h, tile_n_bits, capacity, isect_ids,
+                                      flatten_ids, gsb_stream(stream));
+    if (mean * 3 <= 4096 * 2)
+        return launch_segment_sort<16>(n, dk, tmp, offsets, tile_w * tile_h, tile_n_bits, capacity, isect_ids,
+                                       flatten_ids, gsb_stream(stream));
+    return launch_segment_sort<32>(n, dk, tmp, offsets, tile_w * tile_h, tile_n_bits, capacity, isect_ids,
+                                   flatten_ids, gsb_stream(stream));
 }
