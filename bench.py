@@ -44,6 +44,7 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--map-gauss", type=int, default=500_000)
     ap.add_argument("--no-mapping", action="store_true")
+    ap.add_argument("--map-eager", action="store_true")
     return ap.parse_args()
 
 
@@ -177,8 +178,9 @@ def mapping_leg(args, dev, rank, world):
         mine = [rank % n_views]          # more ranks than views: replicate (never at 1/2/4/8)
     g = sc.to(dev)
     splats = FlatSplats(g.params())
-    opt = FusedAdam([dict(params=[p], lr=DEFAULT_LRS[nm]) for p, nm in zip(splats.params, PARAM_NAMES)])
-    step = MappingStep(splats, opt)
+    opt = FusedAdam([dict(params=[p], lr=DEFAULT_LRS[nm]) for p, nm in zip(splats.params, PARAM_NAMES)],
+                    capturable=True)
+    mstep = MappingStep(splats, opt)
     vm, K = g.viewmats[mine].contiguous(), g.Ks[mine].contiguous()
     gt = target_images(n_views, sc.height, sc.width)[mine].to(dev)
     exposure = torch.zeros(len(mine), 2, device=dev)
@@ -189,15 +191,30 @@ def mapping_leg(args, dev, rank, world):
             dist.barrier()
         torch.cuda.synchronize()
 
+    def eager():
+        return mstep(vm, K, gt, exposure, sc.width, sc.height, n_views).total
+
     for _ in range(3):
-        step(vm, K, gt, exposure, sc.width, sc.height, n_views)
+        eager()
     barrier()
+    # the step is launch-bound at one view per GPU (about 60 launches), so it is replayed as ONE CUDA
+    # graph (NCCL all-reduces included); --map-eager times the plain launches instead
+    run, mode = eager, "eager launches"
+    if not args.map_eager:
+        from gslam_b200.graph import GraphedStep
+        g_step = GraphedStep(eager)
+        run, mode = g_step.replay, "CUDA-graph replay"
+        for _ in range(3):
+            run()
+        barrier()
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
     for e0, e1 in ev:
         e0.record()
-        step(vm, K, gt, exposure, sc.width, sc.height, n_views)
+        run()
         e1.record()
     barrier()
+    if not args.map_eager:
+        g_step.check()
     ms = sum(a.elapsed_time(b) for a, b in ev) / steps
     t = torch.tensor([ms], device=dev, dtype=torch.float64)
     if world > 1:
@@ -207,7 +224,7 @@ def mapping_leg(args, dev, rank, world):
             "unit": "views/s", "ms_per_step": ms, "steps": steps, "n_views": n_views, "n_gauss": n,
             "views_per_rank": len(mine), "scaling": "strong",
             "step": "render RGB+D+beta, exposure + active-NeRF NLL + 0.2 SSIM(valid), backward, "
-                    "flat-gradient all-reduce, isotropic reg, fused Adam + opacity decay (eager launches)"}
+                    "flat-gradient all-reduce, isotropic reg, fused Adam + opacity decay", "timed_loop": mode}
 
 
 def run_ours(args):

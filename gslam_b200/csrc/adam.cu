@@ -18,7 +18,21 @@ struct AdamPack {
 
 __global__ void __launch_bounds__(256)
 adam_multi_kernel(const AdamPack pk, float beta1, float beta2, float eps, float bc1, float rsqrt_bc2,
-                  int decay_tensor, const int32_t* __restrict__ vis_count, int vis_div, float decay) {
+                  int decay_tensor, const int32_t* __restrict__ vis_count, int vis_div, float decay,
+                  int32_t* step_dev) {
+    // Device-side step count (CUDA-graph replays cannot take it as a launch argument): every block
+    // reads step_dev[0] before doing anything; the block that finishes LAST bumps it.
+    __shared__ float s_bc[2];
+    if (step_dev) {
+        if (threadIdx.x == 0) {
+            const int t = *reinterpret_cast<volatile int32_t*>(step_dev) + 1;
+            s_bc[0] = (float)(1.0 - pow((double)beta1, (double)t));
+            s_bc[1] = (float)(1.0 / sqrt(1.0 - pow((double)beta2, (double)t)));
+        }
+        __syncthreads();
+        bc1 = s_bc[0];
+        rsqrt_bc2 = s_bc[1];
+    }
     int ti = 0;
 #pragma unroll
     for (int k = 1; k < ADAM_MAX_TENSORS; ++k)
@@ -39,12 +53,22 @@ adam_multi_kernel(const AdamPack pk, float beta1, float beta2, float eps, float 
         if (ti == decay_tensor && vis_count[i / vis_div] > 1) p *= decay;
         T.param[i] = p;
     }
+    if (step_dev) {
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            __threadfence();
+            if (atomicAdd(step_dev + 1, 1) == (int)gridDim.x - 1) {
+                step_dev[0] += 1;
+                step_dev[1] = 0;
+            }
+        }
+    }
 }
 
 GSB_API int gsb_adam_multi(const gsb_adam_tensor* tensors_host, int n_tensors, float beta1, float beta2,
                            float eps, int step, int decay_tensor, const int32_t* vis_count,
-                           int vis_div, float decay, void* stream) {
-    GSB_CHECK_ARG(n_tensors >= 0 && n_tensors <= ADAM_MAX_TENSORS && step >= 1);
+                           int vis_div, float decay, int32_t* step_dev, void* stream) {
+    GSB_CHECK_ARG(n_tensors >= 0 && n_tensors <= ADAM_MAX_TENSORS && (step >= 1 || step_dev));
     if (n_tensors == 0) return 0;
     GSB_CHECK_ARG(tensors_host);
     GSB_CHECK_ARG(decay_tensor < n_tensors && (decay_tensor < 0 || (vis_count && vis_div >= 1)));
@@ -60,10 +84,11 @@ GSB_API int gsb_adam_multi(const gsb_adam_tensor* tensors_host, int n_tensors, f
     }
     for (int k = n_tensors; k <= ADAM_MAX_TENSORS; ++k) pk.first_block[k] = blocks;
     if (blocks == 0) return 0;
+    if (step < 1) step = 1;     // unused when step_dev is given
     const double bc1 = 1.0 - pow((double)beta1, step), bc2 = 1.0 - pow((double)beta2, step);
     adam_multi_kernel<<<blocks, 256, 0, gsb_stream(stream)>>>(pk, beta1, beta2, eps, (float)bc1,
                                                              (float)(1.0 / sqrt(bc2)), decay_tensor,
-                                                             vis_count, vis_div, decay);
+                                                             vis_count, vis_div, decay, step_dev);
     GSB_LAUNCH_CHECK();
     return 0;
 }

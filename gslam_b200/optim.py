@@ -18,13 +18,24 @@ from ._lib import AdamTensor, call, stream
 
 
 class FusedAdam(torch.optim.Optimizer):
-    def __init__(self, params, lr: float = 1e-3, betas=(0.9, 0.999), eps: float = 1e-8):
+    def __init__(self, params, lr: float = 1e-3, betas=(0.9, 0.999), eps: float = 1e-8,
+                 capturable: bool = False):
+        """capturable=True keeps ONE step counter for all parameters on the device (int32, like
+        torch's capturable Adam keeps `step` on the device), so `step()` can be captured in a CUDA
+        graph and replayed; every parameter is then updated by every call."""
         super().__init__(params, dict(lr=lr, betas=betas, eps=eps))
+        self.capturable = capturable
+        self._dev_step = None        # int32[2] on the parameters' device: {steps done, ticket}
 
     def _state(self, p):
         st = self.state[p]
         if len(st) == 0:
-            st["step"] = torch.tensor(0.0)
+            if self.capturable:
+                if self._dev_step is None:
+                    self._dev_step = torch.zeros(2, dtype=torch.int32, device=p.device)
+                st["step"] = self._dev_step[0:1]
+            else:
+                st["step"] = torch.tensor(0.0)
             st["exp_avg"] = torch.zeros_like(p, memory_format=torch.preserve_format)
             st["exp_avg_sq"] = torch.zeros_like(p, memory_format=torch.preserve_format)
         return st
@@ -43,9 +54,15 @@ class FusedAdam(torch.optim.Optimizer):
                 if not (p.is_cuda and p.dtype == torch.float32 and p.is_contiguous()):
                     raise RuntimeError("FusedAdam needs contiguous float32 CUDA parameters")
                 st = self._state(p)
-                st["step"] += 1
-                key = (int(st["step"]), tuple(group["betas"]), group["eps"])
+                if self.capturable:
+                    key = (0, tuple(group["betas"]), group["eps"])
+                else:
+                    st["step"] += 1
+                    key = (int(st["step"]), tuple(group["betas"]), group["eps"])
                 buckets.setdefault(key, []).append((p, p.grad.contiguous(), st, group["lr"]))
+        if self.capturable and (len(buckets) > 1 or any(len(v) > 8 for v in buckets.values())):
+            raise RuntimeError("FusedAdam(capturable=True) updates all parameters in one launch: "
+                               "at most 8 tensors sharing betas and eps")
         for (step, betas, eps), items in buckets.items():
             for i in range(0, len(items), 8):
                 chunk = items[i:i + 8]
@@ -59,5 +76,6 @@ class FusedAdam(torch.optim.Optimizer):
                         vis_div = max(p.numel() // max(vis_count.numel(), 1), 1)
                 vc = vis_count.data_ptr() if decay_idx >= 0 else None
                 call("gsb_adam_multi", ct.cast(arr, ct.c_void_p), len(chunk), betas[0], betas[1], eps, step,
-                     decay_idx, vc, vis_div, decay, stream())
+                     decay_idx, vc, vis_div, decay,
+                     self._dev_step.data_ptr() if self.capturable else None, stream())
         return loss

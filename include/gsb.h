@@ -183,7 +183,9 @@ int gsb_scale_by_scalar(float* x, int64_t n, const float* grad, void* stream);
 /* K12/K13: ONE launch of Adam over up to 8 tensors (reference gslam/backend.py:559-602 steps
  * seven optimizers) with torch.optim.Adam default semantics; `step` is the 1-based count of this
  * update.  Tensor `decay_tensor` (-1: none) additionally gets the opacity decay of
- * gslam/backend.py:356-359: element i is multiplied by `decay` when vis_count[i / vis_div] > 1. */
+ * gslam/backend.py:356-359: element i is multiplied by `decay` when vis_count[i / vis_div] > 1.
+ * step_dev (NULL, or int32[2] = {updates done so far, 0}) keeps the step count on the device instead:
+ * the launch uses step_dev[0] + 1 and increments it, so a captured CUDA graph can be replayed. */
 typedef struct {
     float* param;
     const float* grad;
@@ -194,7 +196,7 @@ typedef struct {
 } gsb_adam_tensor;
 int gsb_adam_multi(const gsb_adam_tensor* tensors_host, int n_tensors, float beta1, float beta2,
                    float eps, int step, int decay_tensor, const int32_t* vis_count, int vis_div,
-                   float decay, void* stream);
+                   float decay, int32_t* step_dev, void* stream);
 
 #ifdef __cplusplus
 }

@@ -107,8 +107,10 @@ def test_tracking_loss_modes(cuda, kind):
     assert rel_err(eg.grad, er.grad) < 1e-3
 
 
-def test_fused_adam_matches_torch_adam(cuda):
-    """Six tensors with the reference's learning rates (gslam/backend.py:53-58), 5 steps, one launch each."""
+@pytest.mark.parametrize("capturable", [False, True])
+def test_fused_adam_matches_torch_adam(cuda, capturable):
+    """Six tensors with the reference's learning rates (gslam/backend.py:53-58), 5 steps, one launch each;
+    capturable=True keeps the step count on the device (CUDA-graph replay)."""
     g = torch.Generator().manual_seed(0)
     n = 1000
     shapes = [(n, 3), (n, 4), (n, 3), (n,), (n, 3), (n,)]
@@ -117,7 +119,7 @@ def test_fused_adam_matches_torch_adam(cuda):
     ref_p = [p.clone().requires_grad_(True) for p in init]
     ref_opts = [torch.optim.Adam([p], lr=lr) for p, lr in zip(ref_p, lrs)]
     our_p = [p.clone().to(cuda).requires_grad_(True) for p in init]
-    ours = FusedAdam([dict(params=[p], lr=lr) for p, lr in zip(our_p, lrs)])
+    ours = FusedAdam([dict(params=[p], lr=lr) for p, lr in zip(our_p, lrs)], capturable=capturable)
     vis = torch.randint(0, 4, (n,), generator=g, dtype=torch.int32)
     for it in range(5):
         grads = [torch.randn(s, generator=g) for s in shapes]
