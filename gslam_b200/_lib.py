@@ -43,7 +43,7 @@ SIGNATURES = {
     "gsb_composite_fwd": (_i, [_p] * 4 + [_i] * 6 + [_l, _f] + [_p] * 5 + [_p]),
     "gsb_ssim_fwd": (_i, [_p] * 4 + [_i] * 5 + [_p] * 4 + [_p]),
     "gsb_ssim_bwd": (_i, [_p] * 4 + [_i] * 4 + [_p] * 4 + [_f, _p, _p, _i, _p]),
-    "gsb_photo_loss": (_i, [_p, _p, _p, _i, _i, _i, _i, _f, _p, _p, _p, _p]),
+    "gsb_photo_loss": (_i, [_p, _p, _p, _i, _i, _i, _i, _f, _p, _p, _p, _p, _p]),
     "gsb_scale_by_scalar": (_i, [_p, _l, _p, _p]),
     "gsb_adam_multi": (_i, [_p, _i, _f, _f, _f, _i, _i, _p, _i, _f, _p, _p]),
     "gsb_composite_bwd": (_i, [_p] * 4 + [_i] * 6 + [_l] + [_p] * 6 + [_p]),

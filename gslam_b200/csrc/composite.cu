@@ -18,7 +18,7 @@ composite_fwd_kernel(const float4* __restrict__ rec, const int32_t* __restrict__
                      const int32_t* __restrict__ offsets, const float* __restrict__ backgrounds,
                      int n_lin, int width, int height, int tile_w, int tile_h, int64_t n_isects,
                      float min_T, float* __restrict__ render, float* __restrict__ alphas,
-                     int32_t* __restrict__ last_ids, int32_t* __restrict__ n_touched,
+                     int32_t* __restrict__ last_ids, unsigned long long* __restrict__ n_touched,
                      unsigned long long* __restrict__ pair_count) {
     __shared__ WarpStage s_ws[CMP_WARPS];
     __shared__ int32_t s_ids[CMP_WARPS][NSTAGE][RND];
@@ -134,7 +134,7 @@ composite_fwd_kernel(const float4* __restrict__ rec, const int32_t* __restrict__
                 }
                 if (COUNT && lane == k) cnt_reg = n_touch;
             }
-            if (COUNT && cnt_reg > 0) atomicAdd(n_touched + ws.gid[lane], cnt_reg);
+            if (COUNT && cnt_reg > 0) atomicAdd(n_touched + ws.gid[lane], (unsigned long long)cnt_reg);
             __syncwarp();
             if (++stage == NSTAGE) stage = 0;
         }
@@ -167,7 +167,7 @@ composite_fwd_kernel(const float4* __restrict__ rec, const int32_t* __restrict__
 GSB_API int gsb_composite_fwd(const float* rec, const int32_t* flatten_ids, const int32_t* offsets,
                               const float* backgrounds, int C, int N, int width, int height, int tile_w,
                               int tile_h, int64_t n_isects, float visibility_min_T, float* render,
-                              float* alphas, int32_t* last_ids, int32_t* n_touched,
+                              float* alphas, int32_t* last_ids, int64_t* n_touched,
                               int64_t* pair_count, void* stream) {
     (void)N;
     GSB_CHECK_ARG(C >= 0 && width > 0 && height > 0 && tile_w > 0 && tile_h > 0);
@@ -185,7 +185,8 @@ GSB_API int gsb_composite_fwd(const float* rec, const int32_t* flatten_ids, cons
 #define GSB_FWD(COUNT, STATS)                                                                     \
     composite_fwd_kernel<COUNT, STATS><<<grid, CMP_THREADS, 0, gsb_stream(stream)>>>(             \
         r4, flatten_ids, offsets, backgrounds, n_lin, width, height, tile_w, tile_h, n_isects,    \
-        visibility_min_T, render, alphas, last_ids, n_touched, pc)
+        visibility_min_T, render, alphas, last_ids,                                              \
+        reinterpret_cast<unsigned long long*>(n_touched), pc)
     if (n_touched && pc) GSB_FWD(true, true);
     else if (n_touched) GSB_FWD(true, false);
     else if (pc) GSB_FWD(false, true);

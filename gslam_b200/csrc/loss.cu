@@ -191,7 +191,7 @@ GSB_API int gsb_ssim_bwd(const float* img1, const float* img2, const int64_t* st
 __global__ void __launch_bounds__(256)
 photo_loss_kernel(const float* __restrict__ render, const float* __restrict__ gt,
                   const float* __restrict__ exposure, int mode, int HW, float inv_count, float coef,
-                  float* __restrict__ loss_sum, float* __restrict__ v_render,
+                  float* __restrict__ loss_sum, float* __restrict__ loss_out, float* __restrict__ v_render,
                   float* __restrict__ v_exposure) {
     __shared__ float red[8];
     const int cam = blockIdx.y;
@@ -249,10 +249,22 @@ photo_loss_kernel(const float* __restrict__ render, const float* __restrict__ gt
         __syncthreads();
         s = block_sum_256(gb, red); if (threadIdx.x == 0 && s != 0.f) atomicAdd(v_exposure + cam * 2 + 1, s);
     }
+    // the block that finishes last turns the two sums into the loss values, so the caller needs no
+    // scalar arithmetic kernels: loss_out = (coef * photometric, photometric)
+    if (loss_out && threadIdx.x == 0) {
+        __threadfence();
+        const unsigned total = gridDim.x * gridDim.y;
+        if (atomicAdd(reinterpret_cast<unsigned*>(loss_sum + 2), 1u) == total - 1) {
+            __threadfence();
+            const float photo = (atomicAdd(loss_sum, 0.f) + atomicAdd(loss_sum + 1, 0.f)) * inv_count;
+            loss_out[0] = coef * photo;
+            loss_out[1] = photo;
+        }
+    }
 }
 
 GSB_API int gsb_photo_loss(const float* render, const float* gt, const float* exposure, int mode, int C,
-                           int H, int W, float coef, float* loss_sum, float* v_render,
+                           int H, int W, float coef, float* loss_sum, float* loss_out, float* v_render,
                            float* v_exposure, void* stream) {
     GSB_CHECK_ARG(C >= 0 && H > 0 && W > 0 && mode >= 0 && mode <= 3);
     if (C == 0) return 0;
@@ -261,15 +273,17 @@ GSB_API int gsb_photo_loss(const float* render, const float* gt, const float* ex
     dim3 grid((HW + 255) / 256, C);
     photo_loss_kernel<<<grid, 256, 0, gsb_stream(stream)>>>(render, gt, exposure, mode, HW,
                                                             1.0f / ((float)C * (float)HW), coef, loss_sum,
-                                                            v_render, v_exposure);
+                                                            loss_out, v_render, v_exposure);
     GSB_LAUNCH_CHECK();
     return 0;
 }
 
 // v_render[C,H,W,5] *= *grad  (device scalar), used when the fused loss is not the graph root
 __global__ void scale_kernel(float* __restrict__ x, int64_t n, const float* __restrict__ grad) {
+    const float g = *grad;
+    if (g == 1.0f) return;      // loss.backward() on the fused loss itself: nothing to do, no traffic
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) x[i] *= *grad;
+    if (i < n) x[i] *= g;
 }
 
 GSB_API int gsb_scale_by_scalar(float* x, int64_t n, const float* grad, void* stream) {

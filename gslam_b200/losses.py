@@ -74,20 +74,21 @@ def fused_ssim(img1: Tensor, img2: Tensor, padding: str = "same", train: bool = 
 class _PhotometricSSIM(torch.autograd.Function):
     @staticmethod
     def forward(ctx, render, gt, exposure, ssim_weight, mode):
+        ctx.set_materialize_grads(False)
         # render [C,H,W,5] = (r, g, b, depth, beta); gt [C,H,W,3]; exposure [C,2] or None
         assert render.is_cuda and render.is_contiguous() and render.shape[-1] == 5
         gt = gt.contiguous()
         C, H, W, _ = render.shape
         dev = render.device
         exposure_c = exposure.contiguous() if exposure is not None else None
-        loss_sum = torch.zeros(2, dtype=torch.float32, device=dev)
+        loss_sum = torch.zeros(3, dtype=torch.float32, device=dev)     # two sums + the block ticket
+        loss_out = torch.empty(2, dtype=torch.float32, device=dev)     # (weighted, plain) photometric loss
         v_render = torch.empty_like(render)
         need_exp = exposure is not None and ctx.needs_input_grad[2]
         v_exp = torch.zeros(C, 2, dtype=torch.float32, device=dev) if need_exp else None
         call("gsb_photo_loss", ptr(render), ptr(gt), ptr(exposure_c), mode, C, H, W, 1.0 - ssim_weight,
-             ptr(loss_sum), ptr(v_render), ptr(v_exp), stream())
-        photo = (loss_sum[0] + loss_sum[1]) / (C * H * W)
-        total = (1.0 - ssim_weight) * photo
+             ptr(loss_sum), ptr(loss_out), ptr(v_render), ptr(v_exp), stream())
+        total, photo = loss_out[0], loss_out[1]
         ssim = None
         maps = img1 = img2 = None
         if ssim_weight != 0.0:

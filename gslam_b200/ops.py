@@ -44,7 +44,8 @@ def tile_bits(tile_w: int, tile_h: int, n_cameras: int):
 class _Project(torch.autograd.Function):
     @staticmethod
     def forward(ctx, means, quats, log_scales, logit_opacities, logit_colors, log_unc, viewmats, Ks,
-                width, height, eps2d, near_plane, far_plane, radius_clip, tile_w, tile_h):
+                width, height, eps2d, near_plane, far_plane, radius_clip, tile_w, tile_h, tile_counts):
+        ctx.set_materialize_grads(False)    # no zero-fill kernels for the integer outputs' "gradients"
         means, quats, log_scales = _c(means), _c(quats), _c(log_scales)
         logit_opacities, logit_colors, log_unc = _c(logit_opacities), _c(logit_colors), _c(log_unc)
         viewmats, Ks = _c(viewmats), _c(Ks)
@@ -54,7 +55,8 @@ class _Project(torch.autograd.Function):
         tiles = torch.empty(C, N, dtype=torch.int32, device=dev)
         means2d = torch.empty(C, N, 2, dtype=torch.float32, device=dev)
         rec = torch.empty(C, N, REC, dtype=torch.float32, device=dev)
-        tile_counts = torch.zeros(C, tile_h * tile_w, CSTRIDE, dtype=torch.int32, device=dev)
+        if tile_counts is None:
+            tile_counts = torch.zeros(C, tile_h * tile_w, CSTRIDE, dtype=torch.int32, device=dev)
         call("gsb_project_fwd", 
             ptr(means), ptr(quats), ptr(log_scales), ptr(logit_opacities), ptr(logit_colors),
             ptr(log_unc), ptr(viewmats), ptr(Ks), C, N, width, height, eps2d, near_plane, far_plane,
@@ -110,13 +112,14 @@ class _Project(torch.autograd.Function):
         grads = [v_means, v_quats, v_scales, v_opac, v_colors,
                  v_unc if log_unc is not None else None]
         grads = [g if n else None for g, n in zip(grads, need[:6])]
-        return (*grads, v_view, None, None, None, None, None, None, None, None, None)
+        return (*grads, v_view, None, None, None, None, None, None, None, None, None, None)
 
 
 class _Composite(torch.autograd.Function):
     @staticmethod
     def forward(ctx, rec, means2d, flatten_ids, offsets, backgrounds, width, height, tile_w, tile_h,
-                visibility_min_T, count_touched):
+                visibility_min_T, count_touched, n_touched):
+        ctx.set_materialize_grads(False)
         # means2d is not read (the record carries x,y); it is an input only so that its
         # gradient is delivered as a separate autograd edge.
         C, N = rec.shape[0], rec.shape[1]
@@ -127,7 +130,10 @@ class _Composite(torch.autograd.Function):
         render = torch.empty(C, height, width, CH, dtype=torch.float32, device=dev)
         alphas = torch.empty(C, height, width, 1, dtype=torch.float32, device=dev)
         last_ids = torch.empty(C, height, width, dtype=torch.int32, device=dev)
-        n_touched = torch.zeros(C, N, dtype=torch.int32, device=dev) if count_touched else None
+        if not count_touched:
+            n_touched = None
+        elif n_touched is None:
+            n_touched = torch.zeros(C, N, dtype=torch.int64, device=dev)
         call("gsb_composite_fwd", 
             ptr(rec), ptr(flatten_ids), ptr(offsets), ptr(backgrounds), C, N, width, height, tile_w,
             tile_h, n_isects, visibility_min_T, ptr(render), ptr(alphas), ptr(last_ids),
@@ -135,7 +141,7 @@ class _Composite(torch.autograd.Function):
         ctx.save_for_backward(rec, flatten_ids, offsets, backgrounds, alphas, last_ids)
         ctx.dims = (C, N, width, height, tile_w, tile_h, n_isects)
         if n_touched is None:
-            n_touched = torch.zeros(C, N, dtype=torch.int32, device=dev)
+            n_touched = torch.zeros(C, N, dtype=torch.int64, device=dev)
         ctx.mark_non_differentiable(n_touched)
         return render, alphas, n_touched
 
@@ -156,15 +162,29 @@ class _Composite(torch.autograd.Function):
             tile_h, n_isects, ptr(alphas), ptr(last_ids), ptr(v_render), ptr(v_alphas),
             ptr(v_rec), ptr(v_bg), stream())
         # x,y gradients travel on the means2d edge; _Project.backward ignores those two slots of v_rec
-        return v_rec, v_rec[..., 0:2], None, None, v_bg, None, None, None, None, None, None
+        return v_rec, v_rec[..., 0:2], None, None, v_bg, None, None, None, None, None, None, None
 
 
 def project(means, quats, log_scales, logit_opacities, logit_colors, log_unc, viewmats, Ks, width,
-            height, eps2d=0.3, near_plane=0.01, far_plane=1e10, radius_clip=0.0):
+            height, eps2d=0.3, near_plane=0.01, far_plane=1e10, radius_clip=0.0, tile_counts=None):
+    """tile_counts: optional pre-zeroed int32 [C, T, 32] (see ZeroPool)."""
     tile_w, tile_h = math.ceil(width / TILE), math.ceil(height / TILE)
     return _Project.apply(means, quats, log_scales, logit_opacities, logit_colors, log_unc, viewmats,
                           Ks, int(width), int(height), float(eps2d), float(near_plane),
-                          float(far_plane), float(radius_clip), tile_w, tile_h)
+                          float(far_plane), float(radius_clip), tile_w, tile_h, tile_counts)
+
+
+class ZeroPool:
+    """Every zero-initialised integer buffer of one rasterization() call, cleared by ONE fill kernel:
+    tile_counts int32 [C,T,32] | overflow int32 [1] | n_touched int64 [C,N]."""
+
+    def __init__(self, C: int, N: int, T: int, device):
+        n_counts = C * T * CSTRIDE
+        head = n_counts + 2                      # + overflow, + pad to an 8-byte boundary
+        pool = torch.zeros(head + 2 * C * N, dtype=torch.int32, device=device)
+        self.tile_counts = pool[:n_counts].view(C, T, CSTRIDE)
+        self.overflow = pool[n_counts:n_counts + 1]
+        self.n_touched = pool[head:].view(torch.int64).view(C, N)
 
 
 @torch.no_grad()
@@ -240,7 +260,7 @@ last_n_isects: Optional[Tensor] = None
 
 
 @torch.no_grad()
-def bin_tiles(means2d, radii, rec, tile_counts, tile_w, tile_h):
+def bin_tiles(means2d, radii, rec, tile_counts, tile_w, tile_h, overflow=None):
     """K4+K5, tile-binned (csrc/binning.cu): -> isect_ids, flatten_ids, offsets[C*T+1] i32.
 
     Bit-identical to isect_tiles(sort=True) + isect_offset_encode.  In the default
@@ -254,7 +274,8 @@ def bin_tiles(means2d, radii, rec, tile_counts, tile_w, tile_h):
     offsets = torch.empty(C * T + 1, dtype=torch.int32, device=dev)
     cursors = torch.empty(C * T * CSTRIDE, dtype=torch.int32, device=dev)
     n_dev = torch.empty(1, dtype=torch.int64, device=dev)
-    overflow = torch.zeros(1, dtype=torch.int32, device=dev)
+    if overflow is None:
+        overflow = torch.zeros(1, dtype=torch.int32, device=dev)
     call("gsb_tile_scan", ptr(tile_counts), C, tile_w, tile_h, ptr(offsets), ptr(cursors), ptr(n_dev),
          stream())
     cap = isect_capacity if isect_capacity is not None else read_i64(n_dev)
@@ -272,10 +293,11 @@ def bin_tiles(means2d, radii, rec, tile_counts, tile_w, tile_h):
 
 
 def composite(rec, means2d, flatten_ids, offsets, backgrounds, width, height, visibility_min_T=0.5,
-              count_touched=True):
+              count_touched=True, n_touched=None):
+    """-> render [C,H,W,5], alphas [C,H,W,1], n_touched int64 [C,N] (n_touched: optional pre-zeroed buffer)."""
     tile_w, tile_h = math.ceil(width / TILE), math.ceil(height / TILE)
     return _Composite.apply(rec, means2d, flatten_ids, offsets, backgrounds, int(width), int(height),
-                            tile_w, tile_h, float(visibility_min_T), bool(count_touched))
+                            tile_w, tile_h, float(visibility_min_T), bool(count_touched), n_touched)
 
 
 @torch.no_grad()

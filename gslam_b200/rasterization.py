@@ -47,6 +47,19 @@ class RasterizationOutput:
     n_touched: torch.Tensor = None
 
 
+_BG_TAILS: dict = {}
+
+
+def _bg_tail(device, with_beta: bool) -> Tensor:
+    """(depth, beta) background: (0, e) when uncertainties are rendered (reference :253), else (0, 0)."""
+    key = (str(device), with_beta)
+    t = _BG_TAILS.get(key)
+    if t is None:
+        t = torch.tensor([[0.0, math.e if with_beta else 0.0]], dtype=torch.float32, device=device)
+        _BG_TAILS[key] = t
+    return t
+
+
 def _unsupported(what: str):
     raise NotImplementedError(
         f"gslam_b200.rasterization: {what} is outside the subset gslam uses "
@@ -112,29 +125,29 @@ def rasterization(
     tile_width = math.ceil(width / float(tile_size))
     tile_height = math.ceil(height / float(tile_size))
 
+    zeros = ops.ZeroPool(C, N, tile_width * tile_height, means.device)
+
     # K8+K1 (+ tile counting): activations, projection and record packing in one kernel
     radii, means2d, rec, tiles_per_gauss, tile_counts = ops.project(
         means, quats, log_scales, logit_opacities, logit_colors, log_uncertainties, viewmats, Ks,
-        width, height, eps2d, near_plane, far_plane, radius_clip)
+        width, height, eps2d, near_plane, far_plane, radius_clip, tile_counts=zeros.tile_counts)
 
     # K4+K5: counting sort by tile + per-tile depth sort (bit-identical to the upstream
     # emit / stable radix sort / offset-encode chain, which ops.isect_tiles still provides)
     isect_ids, flatten_ids, offsets = ops.bin_tiles(means2d, radii, rec, tile_counts, tile_width,
-                                                    tile_height)
+                                                    tile_height, overflow=zeros.overflow)
     isect_offsets = offsets[:-1].view(C, tile_height, tile_width)
 
     # backgrounds [C,3] -> [C,5] = (r, g, b, 0, e)   (reference :236-255)
     bg5 = None
     if backgrounds is not None:
-        bg5 = torch.zeros(C, ops.CH, dtype=torch.float32, device=means.device)
-        if render_mode != "D":
-            bg5[:, :3] = backgrounds
-        if log_uncertainties is not None:
-            bg5[:, 4] = math.e
+        tail = _bg_tail(means.device, log_uncertainties is not None).expand(C, 2)
+        rgb = backgrounds if render_mode != "D" else torch.zeros_like(backgrounds)
+        bg5 = torch.cat([rgb, tail], dim=1)        # one kernel
 
     # K6
     render, alphas, n_touched = ops.composite(rec, means2d, flatten_ids, offsets, bg5, width,
-                                              height, visibility_min_T)
+                                              height, visibility_min_T, n_touched=zeros.n_touched)
 
     out = RasterizationOutput(
         rgbs=render[..., :3] if render_mode not in ("D",) else None,
@@ -158,7 +171,7 @@ def rasterization(
         depths=rec[..., 9],
         conics=rec[..., 3:6],
         opacities=rec[..., 2],
-        n_touched=n_touched.long(),
+        n_touched=n_touched,
     )
     out.render = render   # [C,H,W,5] (r g b depth beta); input of losses.photometric_ssim_loss
     return out

@@ -132,7 +132,8 @@ int gsb_isect_offsets(const int64_t* isect_ids, int64_t n_isects, int C, int til
 /* K6: per-tile front-to-back compositing (reference gslam/rasterization.py:325-339).
  * offsets holds C*T entries and n_isects closes the last tile; pass n_isects < 0 when
  * offsets has C*T+1 entries (gsb_tile_scan), so that no host-side count is needed.
- * backgrounds[C,5] may be NULL.  n_touched[C,N] i32 must be zeroed by the caller
+ * backgrounds[C,5] may be NULL.  n_touched[C,N] i64 (the reference's dtype,
+ * gslam/rasterization.py:352) must be zeroed by the caller
  * (NULL skips the count).  Outputs render[C,H,W,5], alphas[C,H,W], last_ids[C,H,W].
  * pair_count (NULL in the product path) accumulates P, the number of (pixel,
  * Gaussian) pairs evaluated before each pixel stopped: the work unit of K6/K7
@@ -140,7 +141,7 @@ int gsb_isect_offsets(const int64_t* isect_ids, int64_t n_isects, int C, int til
 int gsb_composite_fwd(const float* rec, const int32_t* flatten_ids, const int32_t* offsets,
                       const float* backgrounds, int C, int N, int width, int height,
                       int tile_w, int tile_h, int64_t n_isects, float visibility_min_T,
-                      float* render, float* alphas, int32_t* last_ids, int32_t* n_touched,
+                      float* render, float* alphas, int32_t* last_ids, int64_t* n_touched,
                       int64_t* pair_count, void* stream);
 
 /* K7: compositing backward.  v_rec[C,N,12] must be zeroed by the caller and is
@@ -172,11 +173,12 @@ int gsb_ssim_bwd(const float* img1, const float* img2, const int64_t* strides1_h
  * exposure[C,2] = (a, b) or NULL; e = rgb * exp(a) + b - gt.
  *   mode 0: mean(sum_ch e^2 / (2 beta^2)) + mean(0.5 ln^2 beta)      (mapping, active-NeRF)
  *   mode 1: mean(sum_ch e^2 beta^-2)   mode 2: mean |e|   mode 3: mean e^2   (tracking)
- * loss_sum[2] (zeroed by the caller) receives the two un-normalised sums; v_render[C,H,W,5]
+ * loss_sum[3] (zeroed by the caller) receives the two un-normalised sums (+ a block ticket);
+ * loss_out[2] (may be NULL) receives (coef * loss, loss), written by the last block; v_render[C,H,W,5]
  * is overwritten with coef * dLoss/drender; v_exposure[C,2] (zeroed; may be NULL) accumulates
  * coef * dLoss/dexposure. */
 int gsb_photo_loss(const float* render, const float* gt, const float* exposure, int mode, int C,
-                   int H, int W, float coef, float* loss_sum, float* v_render,
+                   int H, int W, float coef, float* loss_sum, float* loss_out, float* v_render,
                    float* v_exposure, void* stream);
 int gsb_scale_by_scalar(float* x, int64_t n, const float* grad, void* stream);
 
