@@ -374,11 +374,61 @@ def run_ours(args):
         e2e_step()
         e1.record()
     barrier()
+    ms2_serial = sum(a.elapsed_time(b) for a, b in ev2) / args.steps
+
+    # The same step with the upload double-buffered: step i+1's inputs travel host -> staging on a copy
+    # stream while step i computes; the compute stream then moves staging -> the step's tensors
+    # (device to device) and replays.  Every step still uploads all of its inputs and reads its result
+    # back; only the order of issue changes.
+    copy_stream = torch.cuda.Stream(device=dev)
+    dsts = params + [vm, K, gt]
+    srcs = host + [host_vm, host_K, host_gt]
+    staging = [[torch.empty_like(d.detach()) for d in dsts] for _ in range(2)]
+    up_done = [torch.cuda.Event() for _ in range(2)]
+    slot_free = [torch.cuda.Event() for _ in range(2)]
+
+    def upload(slot):
+        with torch.cuda.stream(copy_stream), torch.no_grad():
+            copy_stream.wait_event(slot_free[slot])
+            for d, h in zip(staging[slot], srcs):
+                d.copy_(h, non_blocking=True)
+            up_done[slot].record(copy_stream)
+
+    def e2e_pipelined(i):
+        slot = i & 1
+        upload(slot ^ 1)                       # next step's inputs
+        main = torch.cuda.current_stream()
+        main.wait_event(up_done[slot])
+        with torch.no_grad():
+            for d, st in zip(dsts, staging[slot]):
+                d.copy_(st, non_blocking=True)
+        slot_free[slot].record(main)
+        loss = gstep.replay()
+        res = torch.cat([loss.detach().view(1), static_vm_grad.view(-1)])
+        res_host.copy_(res, non_blocking=True)
+        main.synchronize()
+
+    for sl in range(2):
+        slot_free[sl].record(torch.cuda.current_stream())
+    upload(0)
+    for i in range(4):
+        e2e_pipelined(i)
+    barrier()
+    ev2 = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+           for _ in range(args.steps)]
+    for i, (e0, e1) in enumerate(ev2):
+        flush_buf.zero_()
+        e0.record()
+        e2e_pipelined(i)
+        e1.record()
+    barrier()
+    copy_stream.synchronize()
     ms2 = sum(a.elapsed_time(b) for a, b in ev2) / args.steps
-    t = torch.tensor([ms2], device=dev, dtype=torch.float64)
+    t = torch.tensor([ms2, ms2_serial], device=dev, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    e2e_value = world * 1e3 / float(t.item())
+    e2e_value = world * 1e3 / float(t[0].item())
+    e2e_serial = world * 1e3 / float(t[1].item())
 
     mapping = None
     if not args.no_mapping:
@@ -437,7 +487,10 @@ def run_ours(args):
                                    + (", independent replicas (tracking does not shard)" if world > 1 else ""),
                        "l2": "256 MiB memset between timed steps, outside each step's event pair",
                        "n_isects": I, "pairs": P},
-            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "how": "pinned host -> staging on a copy stream (double-buffered, overlaps the previous "
+                           "step), staging -> step tensors D2D, graph replay, loss + pose gradient D2H, sync",
+                    "serial_value": e2e_serial},
             "gpu_launches": launches,
             "launch_calls_per_step": launches / args.steps,
             "timed_loop": "CUDA-graph replay of step() (public rasterization() API + loss + backward)",
