@@ -91,16 +91,22 @@ isect_scatter_kernel(const float* __restrict__ means2d, const int32_t* __restric
     }
     const int n_tiles = tile_w * tile_h;
     const uint32_t id = (uint32_t)i;
-    warp_expand_tiles(x0, y0, x1 - x0, cnt, [&](int owner, int tx, int ty, bool active) {
-        uint32_t o_d = __shfl_sync(0xffffffffu, dbits, owner);
-        uint32_t o_id = __shfl_sync(0xffffffffu, id, owner);
-        int o_cam = __shfl_sync(0xffffffffu, cam, owner);
-        if (active) {
-            int pos = atomicAdd(cursors + ((size_t)o_cam * n_tiles + ty * tile_w + tx) * GSB_CSTRIDE, 1);
-            if (pos < capacity) dk[pos] = ((uint64_t)o_d << 32) | o_id;
+    uint64_t word = ((uint64_t)dbits << 32) | id;      // this lane's key, or the owner's in the cooperative part
+    int32_t* cur = cursors + (size_t)cam * n_tiles * GSB_CSTRIDE;
+    const uint64_t my_word = word;
+    int32_t* const my_cur = cur;
+    warp_for_tiles(x0, y0, x1 - x0, cnt,
+        [&](int owner, bool coop) {
+            if (coop) {
+                word = __shfl_sync(0xffffffffu, my_word, owner);
+                cur = reinterpret_cast<int32_t*>(__shfl_sync(0xffffffffu, reinterpret_cast<uint64_t>(my_cur), owner));
+            }
+        },
+        [&](int tx, int ty) {
+            int pos = atomicAdd(cur + (size_t)(ty * tile_w + tx) * GSB_CSTRIDE, 1);
+            if (pos < capacity) dk[pos] = word;
             else *overflow = 1;
-        }
-    });
+        });
 }
 
 GSB_API int gsb_isect_scatter(const float* means2d, const int32_t* radii, const float* rec, int C, int N,

@@ -65,40 +65,40 @@ __device__ __forceinline__ void tile_bbox(float mx, float my, int radius, int ti
     y1 = min(max(0, (int)ceilf(ty + tr)), tile_h);
 }
 
-// Warp-balanced expansion of per-lane tile rectangles.  Every lane of a full warp
-// brings a rectangle (x0, y0, width bw, cnt = bw*bh tiles, cnt may be 0); the
-// warp's total work is dealt out one tile per lane per round, so one large splat
-// cannot serialise its lane.  f(owner_lane, tx, ty, active) is called by ALL
-// lanes each round (so it may shuffle from owner_lane); only `active` lanes own
-// a tile.
-template <typename F>
-__device__ __forceinline__ void warp_expand_tiles(int x0, int y0, int bw, int cnt, F&& f) {
+// Visit every tile of every lane's rectangle (x0, y0, width bw, cnt = bw*bh tiles, cnt may be 0).
+// Lanes with up to TILES_DIRECT tiles (nearly all: the mean is about 8) walk their own rectangle
+// with no cross-lane traffic -- a shuffle-based balanced expansion costs a five-deep dependent
+// shuffle chain per 32 tiles, which made the binning kernels latency-bound.  A lane with a larger
+// rectangle hands it to the whole warp afterwards, one tile per lane per step, so one huge splat
+// cannot serialise its lane.  f(tx, ty, owner) is called for each tile by the lane that visits it;
+// owner is the lane that owns the rectangle (== the calling lane in the direct part), so per-owner
+// values can be fetched with __shfl_sync(..., owner) -- in the cooperative part ALL lanes call
+// f_coop_begin(owner) first (warp-uniform) to let the caller broadcast what it needs.
+#define TILES_DIRECT 48
+template <typename F, typename B>
+__device__ __forceinline__ void warp_for_tiles(int x0, int y0, int bw, int cnt, B&& begin_owner, F&& f) {
     const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31;
-    int incl = cnt;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        int y = __shfl_up_sync(full, incl, o);
-        if (lane >= o) incl += y;
-    }
-    const int total = __shfl_sync(full, incl, 31);
-    const int excl = incl - cnt;
-    for (int base = 0; base < total; base += 32) {
-        const int k = base + lane;
-        const bool active = k < total;
-        // owner = last lane whose exclusive prefix is <= k (binary search over lanes)
-        int lo = 0;
-#pragma unroll
-        for (int step = 16; step > 0; step >>= 1) {
-            int probe = __shfl_sync(full, excl, lo + step);
-            if (probe <= k) lo += step;
+    const bool big = cnt > TILES_DIRECT;
+    if (!big && cnt > 0) {
+        begin_owner(lane, false);
+        int tx = x0, ty = y0;
+        const int xe = x0 + bw;
+        for (int t = 0; t < cnt; ++t) {
+            f(tx, ty);
+            if (++tx == xe) { tx = x0; ++ty; }
         }
-        const int o_excl = __shfl_sync(full, excl, lo);
-        const int o_x0 = __shfl_sync(full, x0, lo);
-        const int o_y0 = __shfl_sync(full, y0, lo);
-        const int o_bw = max(__shfl_sync(full, bw, lo), 1);
-        const int local = active ? k - o_excl : 0;
-        const int dy = local / o_bw;
-        f(lo, o_x0 + (local - dy * o_bw), o_y0 + dy, active);
+    }
+    unsigned bigmask = __ballot_sync(full, big);
+    while (bigmask) {
+        const int src = __ffs(bigmask) - 1;
+        bigmask &= bigmask - 1;
+        const int o_x0 = __shfl_sync(full, x0, src), o_y0 = __shfl_sync(full, y0, src);
+        const int o_bw = max(__shfl_sync(full, bw, src), 1), o_cnt = __shfl_sync(full, cnt, src);
+        begin_owner(src, true);
+        for (int t = lane; t < o_cnt; t += 32) {
+            const int dy = t / o_bw;
+            f(o_x0 + (t - dy * o_bw), o_y0 + dy);
+        }
     }
 }

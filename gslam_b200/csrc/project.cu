@@ -188,8 +188,8 @@ project_fwd_kernel(const float* __restrict__ means, const float* __restrict__ qu
             }
             if (tile_counts) {
                 int32_t* tc = tile_counts + (size_t)(c0 + ci) * tile_w * tile_h * GSB_CSTRIDE;
-                warp_expand_tiles(x0, y0, x1 - x0, cnt, [&](int, int tx, int ty, bool active) {
-                    if (active) atomicAdd(tc + (size_t)(ty * tile_w + tx) * GSB_CSTRIDE, 1);
+                warp_for_tiles(x0, y0, x1 - x0, cnt, [](int, bool) {}, [&](int tx, int ty) {
+                    atomicAdd(tc + (size_t)(ty * tile_w + tx) * GSB_CSTRIDE, 1);
                 });
             }
         }
