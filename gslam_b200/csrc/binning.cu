@@ -109,6 +109,68 @@ isect_scatter_kernel(const float* __restrict__ means2d, const int32_t* __restric
         });
 }
 
+// Same scatter with the slot hand-out done per CTA: a CTA takes a contiguous chunk of one camera's
+// Gaussians, histograms their tiles in shared memory, reserves each tile's share of the segment with
+// ONE returning global atomic per (CTA, tile) -- all independent, issued side by side -- and then
+// ranks its keys inside the reserved ranges with shared-memory atomics.  The per-key returning
+// global atomic of the kernel above (whose round trip bounds it) is gone; the order inside a
+// segment is arbitrary either way, the segment sort fixes it.
+#define SCL_THREADS 1024
+template <int GPT>
+__global__ void __launch_bounds__(SCL_THREADS)
+isect_scatter_local_kernel(const float* __restrict__ means2d, const int32_t* __restrict__ radii,
+                           const float* __restrict__ rec, int N, int tile_w, int tile_h,
+                           int32_t* __restrict__ cursors, int64_t capacity, uint64_t* __restrict__ dk,
+                           int32_t* __restrict__ overflow) {
+    extern __shared__ int32_t s_tiles[];
+    const int n_tiles = tile_w * tile_h;
+    int32_t* const hist = s_tiles;              // count, later the running rank
+    int32_t* const base = s_tiles + n_tiles;    // first reserved slot of this CTA in the tile's segment
+    const int tid = threadIdx.x, cam = blockIdx.y;
+    for (int t = tid; t < n_tiles; t += SCL_THREADS) hist[t] = 0;
+    __syncthreads();
+    int x0[GPT], y0[GPT], bw[GPT], cnt[GPT];
+    uint64_t word[GPT];
+#pragma unroll
+    for (int g = 0; g < GPT; ++g) {
+        const int n = (blockIdx.x * GPT + g) * SCL_THREADS + tid;
+        const int64_t i = (int64_t)cam * N + n;
+        const int r = (n < N) ? radii[i] : 0;
+        x0[g] = y0[g] = bw[g] = cnt[g] = 0; word[g] = 0;
+        if (r > 0) {
+            const float2 m = reinterpret_cast<const float2*>(means2d)[i];
+            int x1, y1;
+            tile_bbox(m.x, m.y, r, tile_w, tile_h, x0[g], x1, y0[g], y1);
+            bw[g] = x1 - x0[g];
+            cnt[g] = bw[g] * (y1 - y0[g]);
+            word[g] = ((uint64_t)__float_as_uint(rec[i * GSB_REC + 9]) << 32) | (uint32_t)i;
+        }
+    }
+#pragma unroll
+    for (int g = 0; g < GPT; ++g)
+        warp_for_tiles(x0[g], y0[g], bw[g], cnt[g], [](int, bool) {},
+                       [&](int tx, int ty) { atomicAdd(&hist[ty * tile_w + tx], 1); });
+    __syncthreads();
+    int32_t* const cur = cursors + (size_t)cam * n_tiles * GSB_CSTRIDE;
+    for (int t = tid; t < n_tiles; t += SCL_THREADS) {
+        const int c = hist[t];
+        if (c) { base[t] = atomicAdd(cur + (size_t)t * GSB_CSTRIDE, c); hist[t] = 0; }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int g = 0; g < GPT; ++g) {
+        uint64_t w = word[g];
+        warp_for_tiles(x0[g], y0[g], bw[g], cnt[g],
+            [&](int owner, bool coop) { if (coop) w = __shfl_sync(0xffffffffu, word[g], owner); },
+            [&](int tx, int ty) {
+                const int t = ty * tile_w + tx;
+                const int pos = base[t] + atomicAdd(&hist[t], 1);
+                if (pos < capacity) dk[pos] = w;
+                else *overflow = 1;
+            });
+    }
+}
+
 GSB_API int gsb_isect_scatter(const float* means2d, const int32_t* radii, const float* rec, int C, int N,
                               int tile_w, int tile_h, int32_t* cursors, int64_t capacity,
                               int64_t* depth_id, int32_t* overflow, void* stream) {
@@ -117,6 +179,24 @@ GSB_API int gsb_isect_scatter(const float* means2d, const int32_t* radii, const 
     GSB_CHECK_ARG(means2d && radii && rec && cursors && overflow);
     GSB_CHECK_ARG(capacity == 0 || depth_id);
     GSB_CHECK_ARG(CN < ((int64_t)1 << 31) && capacity < ((int64_t)1 << 31));
+    const size_t smem = (size_t)tile_w * tile_h * 2 * sizeof(int32_t);
+    if (smem <= 96 * 1024 && C <= 65535) {
+        // chunk = 2048 Gaussians of one camera: ~10 keys per (CTA, tile) at SLAM densities
+        // (measured: 1024 the same, 4096 slower -- too few CTAs)
+        constexpr int GPT = 2;
+        static bool attr_set = false;
+        if (!attr_set) {
+            GSB_CUDA(cudaFuncSetAttribute(isect_scatter_local_kernel<GPT>,
+                                          cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+            attr_set = true;
+        }
+        dim3 grid((N + SCL_THREADS * GPT - 1) / (SCL_THREADS * GPT), C);
+        isect_scatter_local_kernel<GPT><<<grid, SCL_THREADS, smem, gsb_stream(stream)>>>(
+            means2d, radii, rec, N, tile_w, tile_h, cursors, capacity,
+            reinterpret_cast<uint64_t*>(depth_id), overflow);
+        GSB_LAUNCH_CHECK();
+        return 0;
+    }
     int blocks = (int)((CN + 255) / 256);
     isect_scatter_kernel<<<blocks, 256, 0, gsb_stream(stream)>>>(
         means2d, radii, rec, CN, N, tile_w, tile_h, cursors, capacity,
