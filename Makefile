@@ -6,6 +6,10 @@ OBJS := $(patsubst $(SRC_DIR)/%.cu,build/%.o,$(SRCS))
 NVFLAGS := -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 \
            -Xcompiler -fPIC,-fvisibility=hidden -Xptxas -v --expt-relaxed-constexpr
 LIB := gslam_b200/libgsb.so
+# make TRACE=1: per-unit timing trace of the compositing kernels (tools/trace_units.py)
+ifdef TRACE
+NVFLAGS += -DGSB_TRACE
+endif
 
 all: $(LIB)
 

@@ -10,7 +10,19 @@
 //   phase 2 (predicated): blend, transmittance update, stop / n_touched bookkeeping.
 // The conic is pre-scaled by log2(e) at staging so alpha = opacity * ex2(-sigma')
 // is one FMUL + MUFU.EX2.
+//
+// Residency: 64 registers and 5 KB of shared memory per one-warp CTA put the SM's limit of 32
+// CTAs in charge.  Measured alternatives (tools/trace_units.py): fewer resident
+// warps are slower at every setting (12/16/20/24 per SM: 90/83/81/82 us against 78), and two-warp
+// CTAs squeezed to 56 registers to make all 4800 units of a 640x480 view resident spill and lose
+// more than the missing second wave gains.
+#define PPT 2
+#define CMP_WARPS 1
 #include "composite.cuh"
+#ifdef GSB_TRACE
+#include "trace.cuh"
+GSB_TRACE_DEFINE(g_trace_fwd, gsb_debug_trace_fwd)
+#endif
 
 template <bool COUNT, bool STATS>
 __global__ void __launch_bounds__(CMP_THREADS)
@@ -27,8 +39,13 @@ composite_fwd_kernel(const float4* __restrict__ rec, const int32_t* __restrict__
     const int unit = blockIdx.x * CMP_WARPS + warp;
     if (unit >= n_lin * UNITS_PER_TILE) return;
     const Unit u = decode_unit(unit, lane, tile_w, tile_w * tile_h);
+#ifdef GSB_TRACE
+    const unsigned long long t_begin = gsb_gtimer();
+    int n_kept_total = 0;
+#endif
     WarpStage& ws = s_ws[warp];
-    const unsigned k_base = smem_addr(ws.k0);
+    unsigned k_base = smem_addr(ws.raw);        // shared-window address of ring slot `stage`
+    const unsigned k_end = k_base + NSTAGE * STAGE_BYTES;
     const float pxf = (float)u.bx + 0.5f, pyf = (float)u.by + 0.5f;
 
     const TileRange rg = tile_range(offsets, u.lin, n_lin, n_isects);
@@ -78,17 +95,22 @@ composite_fwd_kernel(const float4* __restrict__ rec, const int32_t* __restrict__
             const int li = rg.start + r * RND + lane;
             int n_keep;
             {
-                const float4* raw = &ws.raw[stage][lane * 3];
+                float4* slot = ws.raw[stage];
+                const float4 r0 = slot[lane * 3], r1 = slot[lane * 3 + 1], r2 = slot[lane * 3 + 2];
+                __syncwarp();       // every lane holds its record: the slot may be overwritten
                 float4 o0, o1, o2;
-                const bool keep = (li < rg.end) && stage_and_cull(raw[0], raw[1], raw[2], u.rc, li, o0, o1, o2);
+                const bool keep = stage_and_cull(r0, r1, r2, u.rc, li, o0, o1, o2) && (li < rg.end);
                 const unsigned m = __ballot_sync(full, keep);
                 n_keep = __popc(m);
                 if (keep) {
                     const int pos = __popc(m & ((1u << lane) - 1u));
-                    ws.k0[pos] = o0; ws.k1[pos] = o1; ws.k2[pos] = o2;
+                    slot[pos] = o0; slot[RND + pos] = o1; slot[2 * RND + pos] = o2;
                     if (COUNT) ws.gid[pos] = s_ids[warp][stage][lane];
                 }
             }
+#ifdef GSB_TRACE
+            n_kept_total += n_keep;
+#endif
             __syncwarp();
             // ---- composite the kept entries ----------------------------------------------------
             int cnt_reg = 0;    // lane k: pixels that counted kept entry k as "touched"
@@ -136,7 +158,8 @@ composite_fwd_kernel(const float4* __restrict__ rec, const int32_t* __restrict__
             }
             if (COUNT && cnt_reg > 0) atomicAdd(n_touched + ws.gid[lane], (unsigned long long)cnt_reg);
             __syncwarp();
-            if (++stage == NSTAGE) stage = 0;
+            k_base += STAGE_BYTES;
+            if (++stage == NSTAGE) { stage = 0; k_base = k_end - NSTAGE * STAGE_BYTES; }
         }
         cp_async_wait<0>();
     }
@@ -158,6 +181,9 @@ composite_fwd_kernel(const float4* __restrict__ rec, const int32_t* __restrict__
         // P: entries walked while the pixel was still accumulating (the stopping one included)
         if (STATS) visited += stop_at[j] >= 0 ? stop_at[j] - rg.start + 1 : n;
     }
+#ifdef GSB_TRACE
+    gsb_trace_unit(g_trace_fwd, unit, lane, t_begin, n, n_kept_total);
+#endif
     if (STATS) {
         int v = __reduce_add_sync(full, visited);
         if (lane == 0 && v) atomicAdd(pair_count, (unsigned long long)v);

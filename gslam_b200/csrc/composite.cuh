@@ -1,19 +1,22 @@
 // Definitions shared by the compositing forward and backward kernels.
 //
-// Work decomposition (both directions): ONE WARP (= one CTA) owns one 8x8 quarter-tile and
-// walks the tile's depth-sorted list on its own -- no CTA barrier anywhere.  Every thread owns
-// TWO pixels: slot j of lane l is pixel (l & 7, (l >> 3) + 4 j) of the quarter-tile.  Small units
-// keep ~8 of them per SM sub-partition (latency hiding, load balance: the hardware CTA scheduler
-// hands out the tail of the grid dynamically) and make the culling below sharper.
+// Work decomposition (both directions): ONE WARP (= one CTA) owns one UNIT of a 16x16 tile and
+// walks the tile's depth-sorted list on its own -- no CTA barrier anywhere.  The including .cu picks
+// the unit with PPT (pixels per thread) before including this header:
+//   PPT 2: 8x8 quarter-tile, slot j of lane l is pixel (l & 7, (l >> 3) + 4 j)   -- forward kernel
+//   PPT 4: 16x8 half-tile, slots are the four 8x4 blocks                        -- backward kernel
+// Small units keep many of them per SM (latency hiding; the hardware CTA scheduler hands out the
+// tail of the grid dynamically) and make the culling below sharper; larger ones amortise the
+// per-entry work over more pixels and need fewer slots.
 //
 // The list is consumed in rounds of 32 entries.  Splat records (48 B) are gathered
 // from HBM/L2 into a three-stage shared-memory ring with cp.async (LDGSTS, 3 x 16 B per
 // lane), two rounds ahead of use; the ids that address them are prefetched one round
 // earlier still.  When a round lands, every lane takes one record, pre-scales the
 // conic by log2(e), and runs an EXACT ellipse-vs-rectangle test: the minimum of the
-// quadratic form over the quarter-tile's pixel-centre rectangle is compared with
+// quadratic form over the unit's pixel-centre rectangle is compared with
 // log2(255 * opacity), the largest exponent that can still reach alpha >= 1/255.
-// Entries that cannot touch the quarter-tile (about 60 % of gsplat's 3-sigma bounding-
+// Entries that cannot touch the unit (50-60 % of gsplat's 3-sigma bounding-
 // square list) are dropped by a ballot/popc compaction, so the per-pixel loop only
 // sees splats that matter.
 #pragma once
@@ -24,11 +27,15 @@
 #define T_STOP 1e-4f
 #define LOG2E 1.4426950408889634f
 
-#define CMP_WARPS 1            // independent quarter-tile workers per CTA
+#ifndef CMP_WARPS
+#define CMP_WARPS 1            // independent workers (warps) per CTA; set by the including .cu
+#endif
 #define CMP_THREADS (32 * CMP_WARPS)
 #define RND 32                 // list entries per round (one per lane)
 #define NSTAGE 3               // cp.async ring depth
+#ifndef PPT
 #define PPT 2                  // pixels per thread: 2 -> 8x8 quarter-tile units, 4 -> 16x8 half-tiles
+#endif
 #if PPT == 2
 #define UNITS_PER_TILE 4
 #define UNIT_W 8
@@ -73,7 +80,8 @@ __device__ __forceinline__ float4 lds128(unsigned addr) {
                  : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr) : "memory");
     return v;
 }
-#define K_PLANE_BYTES (RND * 16)   // k0, k1, k2 are contiguous in WarpStage
+#define K_PLANE_BYTES (RND * 16)   // the three planes of kept entries are contiguous
+#define STAGE_BYTES (RND * 48)     // one ring slot
 
 // Shared-window address of p, pinned in a register (the opaque move stops the compiler from
 // re-deriving it from SR_CgaCtaId inside the hot loop).
@@ -83,16 +91,19 @@ __device__ __forceinline__ unsigned smem_addr(const void* p) {
     return r;
 }
 
-// Per-warp staging area.
+// Per-warp staging area.  A ring slot first holds the gathered records, lane-major (48 B per lane);
+// once every lane has its record in registers the SAME slot is overwritten with the compacted
+// planes of the kept entries:
+//   plane 0 [0, RND):       x, y, a', b'
+//   plane 1 [RND, 2 RND):   c', list index (int bits), opacity, r
+//   plane 2 [2 RND, 3 RND): g, b, depth, beta
+// (in place: 4.6 KB per warp instead of 6.1 KB, which is what decides how many units fit an SM)
 struct __align__(16) WarpStage {
-    float4 raw[NSTAGE][RND * 3];   // ring of gathered records, lane-major (48 B per lane)
-    float4 k0[RND];                // kept entries: x, y, a', b'
-    float4 k1[RND];                //               c', list index (int bits), opacity, r
-    float4 k2[RND];                //               g, b, depth, beta
-    int32_t gid[RND];              //               flatten id (camera * N + gaussian)
+    float4 raw[NSTAGE][RND * 3];
+    int32_t gid[RND];              // flatten id (camera * N + gaussian) of the kept entries
 };
 
-// The quarter-tile's pixel-centre rectangle.
+// The unit's pixel-centre rectangle.
 struct Rect {
     float x0, x1, y0, y1;
 };

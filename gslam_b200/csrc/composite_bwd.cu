@@ -6,10 +6,10 @@
 // each splat is a running suffix sum.
 //
 // Same decomposition as the forward kernel (composite.cuh): one independent warp per
-// 8x8 quarter-tile, TWO pixels per thread, cp.async-staged rounds of 32 entries that are
+// unit (16x8 half-tile, FOUR pixels per thread), cp.async-staged rounds of 32 entries that are
 // culled against the unit and compacted before the per-pixel loop.  Consequences:
 //   * a thread sums the gradients of its pixels in registers before any
-//     cross-lane traffic, so the warp reduction runs once per 64 pixels;
+//     cross-lane traffic, so the warp reduction runs once per 128 pixels;
 //   * a slot is a compact 8x4 block, so small splats leave whole slots without a
 //     hit and the warp skips their gradient math after one vote;
 //   * the 11 sums of an entry cross the warp through shared memory: 11 conflict-free stores, four
@@ -18,7 +18,21 @@
 //     (behind . v_render) instead of a 5-vector;
 //   * per (unit, kept Gaussian) one lane issues three float4 atomics to v_rec,
 //     32 Gaussians at a time.
+//
+// Residency: 16x8 half-tile units (four pixels per thread) here, although the forward kernel uses
+// 8x8 -- at 91 registers and 10.6 KB of shared memory 21 warps fit an SM, so all 2400 units of a
+// 640x480 view are resident at once; with 8x8 units (4800 of them, 21 per SM) the second wave
+// drains through a half-empty machine and costs more than the blunter culling of the larger unit
+// (121 us against 113; fewer resident warps are slower still -- DESIGN.md 4.3).
+#ifndef PPT
+#define PPT 4
+#endif
+#define CMP_WARPS 1
 #include "composite.cuh"
+#ifdef GSB_TRACE
+#include "trace.cuh"
+GSB_TRACE_DEFINE(g_trace_bwd, gsb_debug_trace_bwd)
+#endif
 
 #define GRAD_N 11                       // gradient sums per (unit, Gaussian)
 #define RED_STRIDE 36                   // floats per row of the reduction tile: 32 lanes + 4 pad, so the
@@ -45,9 +59,14 @@ composite_bwd_kernel(const float4* __restrict__ rec, const int32_t* __restrict__
     const int unit = blockIdx.x * CMP_WARPS + warp;
     if (unit >= n_lin * UNITS_PER_TILE) return;
     const Unit u = decode_unit(unit, lane, tile_w, tile_w * tile_h);
+#ifdef GSB_TRACE
+    const unsigned long long t_begin = gsb_gtimer();
+    int n_kept_total = 0;
+#endif
     WarpStage& ws = s_ws[warp];
     float (*acc_rows)[12] = s_acc[warp];
-    const unsigned k_base = smem_addr(ws.k0);
+    unsigned k_base = smem_addr(ws.raw);        // shared-window address of ring slot `stage`
+    const unsigned k_end = k_base + NSTAGE * STAGE_BYTES;
     const unsigned red_base = smem_addr(s_red[warp]);
     const float pxf = (float)u.bx + 0.5f, pyf = (float)u.by + 0.5f;
 
@@ -123,18 +142,23 @@ composite_bwd_kernel(const float4* __restrict__ rec, const int32_t* __restrict__
         // ---- cull + compact ---------------------------------------------------------------
         const int li = rg.start + r * RND + lane;
         int n_keep;
+        float4* const slot = ws.raw[stage];
         {
-            const float4* raw = &ws.raw[stage][lane * 3];
+            const float4 r0 = slot[lane * 3], r1 = slot[lane * 3 + 1], r2 = slot[lane * 3 + 2];
+            __syncwarp();       // every lane holds its record: the slot may be overwritten
             float4 o0, o1, o2;
-            const bool keep = (li < range_end) && stage_and_cull(raw[0], raw[1], raw[2], u.rc, li, o0, o1, o2);
+            const bool keep = stage_and_cull(r0, r1, r2, u.rc, li, o0, o1, o2) && (li < range_end);
             const unsigned m = __ballot_sync(full, keep);
             n_keep = __popc(m);
             if (keep) {
                 const int pos = __popc(m & ((1u << lane) - 1u));
-                ws.k0[pos] = o0; ws.k1[pos] = o1; ws.k2[pos] = o2;
+                slot[pos] = o0; slot[RND + pos] = o1; slot[2 * RND + pos] = o2;
                 ws.gid[pos] = s_ids[warp][stage][lane];
             }
         }
+#ifdef GSB_TRACE
+        n_kept_total += n_keep;
+#endif
         __syncwarp();
         unsigned wrote = 0;      // bit k: kept entry k produced a gradient row
         unsigned red_flip = 0;
@@ -216,8 +240,8 @@ composite_bwd_kernel(const float4* __restrict__ rec, const int32_t* __restrict__
             const float4* a = reinterpret_cast<const float4*>(&acc_rows[lane][0]);
             float4 a0 = a[0], a1 = a[1], a2 = a[2];
             // finish with this entry's conic: d sigma'/d(x,y) = (2a'dx + b'dy, b'dx + 2c'dy), sigma' = sigma log2(e)
-            const float4 c0 = ws.k0[lane];
-            const float cc = ws.k1[lane].x;
+            const float4 c0 = slot[lane];
+            const float cc = slot[RND + lane].x;
             const float sx = a0.x * (1.0f / LOG2E), sy = a0.y * (1.0f / LOG2E);
             a0.x = 2.f * c0.z * sx + c0.w * sy;
             a0.y = c0.w * sx + 2.f * cc * sy;
@@ -230,9 +254,13 @@ composite_bwd_kernel(const float4* __restrict__ rec, const int32_t* __restrict__
             atomicAdd(dst + 2, a2);
         }
         __syncwarp();
-        if (++stage == NSTAGE) stage = 0;
+        k_base += STAGE_BYTES;
+        if (++stage == NSTAGE) { stage = 0; k_base = k_end - NSTAGE * STAGE_BYTES; }
     }
     cp_async_wait<0>();
+#ifdef GSB_TRACE
+    gsb_trace_unit(g_trace_bwd, unit, lane, t_begin, range_end - rg.start, n_kept_total);
+#endif
 }
 
 GSB_API int gsb_composite_bwd(const float* rec, const int32_t* flatten_ids, const int32_t* offsets,
