@@ -453,6 +453,12 @@ def run_ours(args):
             "gsb_photo_loss": (20 + 12 + 20) * px,
             "gsb_scale_by_scalar": 40 * px,
         }
+        # DRAM bytes per launch from the committed `ncu --set full` capture (tools/ncu_traffic.py)
+        traffic = {}
+        tpath = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "traffic.json")
+        if os.path.exists(tpath) and n == 200_000:
+            with open(tpath) as f:
+                traffic = json.load(f).get("dram_bytes_per_launch", {})
         stages = []
         for name, (calls, msk) in sorted(kt.items(), key=lambda kv: -kv[1][1]):
             if name not in alg:
@@ -460,7 +466,7 @@ def run_ours(args):
             ach = alg[name] / (msk * 1e-3) / 1e9
             stages.append({"kernel": name, "ms": round(msk, 5), "bound": "hbm", "achieved": round(ach, 2),
                            "peak": hbm, "unit": "GB/s", "frac": round(ach / hbm, 5),
-                           "algorithmic_bytes": alg[name]})
+                           "algorithmic_bytes": alg[name], "traffic": traffic.get(name)})
         # FP32 view of the compositing kernels: pairs evaluated x FMA-class instructions per pair
         fp32_peak = 148 * 128 * sm_max * 1e6          # FMA lanes/s
         for st in stages:
@@ -476,7 +482,7 @@ def run_ours(args):
         roofline = None
         if dom:
             roofline = {"kernel": dom["kernel"], "bound": "hbm", "achieved": dom["achieved"], "peak": hbm,
-                        "unit": "GB/s", "frac": dom["frac"], "traffic": None, "peak_source": which,
+                        "unit": "GB/s", "frac": dom["frac"], "traffic": dom["traffic"], "peak_source": which,
                         "ms_per_launch": dom["ms"]}
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,

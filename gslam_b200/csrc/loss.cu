@@ -186,7 +186,7 @@ GSB_API int gsb_ssim_bwd(const float* img1, const float* img2, const int64_t* st
 //   mode 2  'l1'                      mean over pixels and channels of |e|
 //   mode 3  'mse'                     mean over pixels and channels of e^2
 // e = rgb * exp(a_c) + b_c - gt (exposure[C,2] = (a, b); NULL = identity).
-// grid (ceil(H*W/256), C)
+// grid (min(ceil(H*W/256), ~4 CTAs per SM / C), C), chunks of 256 pixels strided over the CTAs
 // ---------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
 photo_loss_kernel(const float* __restrict__ render, const float* __restrict__ gt,
@@ -194,50 +194,88 @@ photo_loss_kernel(const float* __restrict__ render, const float* __restrict__ gt
                   float* __restrict__ loss_sum, float* __restrict__ loss_out, float* __restrict__ v_render,
                   float* __restrict__ v_exposure) {
     __shared__ float red[8];
+    // the CTA's 256 pixels pass through shared memory so that global traffic is 16-byte and
+    // coalesced; a thread then reads its own pixel at stride 5 / 3 floats (conflict-free)
+    __shared__ __align__(16) float s_r[256 * GSB_CH];
+    __shared__ __align__(16) float s_g[256 * 3];
     const int cam = blockIdx.y;
-    const int p = blockIdx.x * 256 + threadIdx.x;
     float ea = 1.f, eb = 0.f;
     if (exposure) { ea = expf(exposure[cam * 2]); eb = exposure[cam * 2 + 1]; }
     float t1 = 0.f, t2 = 0.f, ga = 0.f, gb = 0.f;
+    // a CTA walks several 256-pixel chunks and keeps its sums in registers: the loss sums are ONE
+    // address for the whole grid, and a few hundred CTAs queueing on it cost more than the image traffic
+    for (int p0 = blockIdx.x * 256; p0 < HW; p0 += gridDim.x * 256) {
+    const int p = p0 + threadIdx.x;
+    const int n_px = min(256, HW - p0);
+    const size_t pix0 = (size_t)cam * HW + p0;
+    const bool vec = (HW & 3) == 0 && n_px == 256 &&
+                     ((reinterpret_cast<uintptr_t>(render) | reinterpret_cast<uintptr_t>(gt) |
+                       reinterpret_cast<uintptr_t>(v_render)) & 15) == 0;
+    {
+        // pix0 * 20 B and pix0 * 12 B are multiples of 16 when p0 and HW are multiples of 4
+        const float* rsrc = render + pix0 * GSB_CH;
+        const float* gsrc = gt + pix0 * 3;
+        if (vec) {
+            for (int i = threadIdx.x; i < 256 * GSB_CH / 4; i += 256)
+                reinterpret_cast<float4*>(s_r)[i] = reinterpret_cast<const float4*>(rsrc)[i];
+            if (threadIdx.x < 256 * 3 / 4)
+                reinterpret_cast<float4*>(s_g)[threadIdx.x] = reinterpret_cast<const float4*>(gsrc)[threadIdx.x];
+        } else {
+            for (int i = threadIdx.x; i < n_px * GSB_CH; i += 256) s_r[i] = rsrc[i];
+            for (int i = threadIdx.x; i < n_px * 3; i += 256) s_g[i] = gsrc[i];
+        }
+    }
+    __syncthreads();
     if (p < HW) {
-        const size_t pix = (size_t)cam * HW + p;
-        const float* r = render + pix * GSB_CH;
-        const float* g = gt + pix * 3;
+        float* r = s_r + threadIdx.x * GSB_CH;
+        const float* g = s_g + threadIdx.x * 3;
         const float beta = r[4];
         float e[3], vr[3], vbeta = 0.f, se = 0.f;
 #pragma unroll
         for (int k = 0; k < 3; ++k) { e[k] = r[k] * ea + eb - g[k]; se += e[k] * e[k]; }
         if (mode == 0) {
             const float ib2 = 1.0f / (beta * beta), lb = logf(beta);
-            t1 = 0.5f * se * ib2; t2 = 0.5f * lb * lb;
+            t1 += 0.5f * se * ib2; t2 += 0.5f * lb * lb;
 #pragma unroll
             for (int k = 0; k < 3; ++k) vr[k] = e[k] * ib2;
             vbeta = (-se * ib2 + lb) / beta;
         } else if (mode == 1) {
             const float ib2 = 1.0f / (beta * beta);
-            t1 = se * ib2;
+            t1 += se * ib2;
 #pragma unroll
             for (int k = 0; k < 3; ++k) vr[k] = 2.f * e[k] * ib2;
             vbeta = -2.f * se * ib2 / beta;
         } else if (mode == 2) {
-            t1 = (fabsf(e[0]) + fabsf(e[1]) + fabsf(e[2])) * (1.f / 3.f);
+            t1 += (fabsf(e[0]) + fabsf(e[1]) + fabsf(e[2])) * (1.f / 3.f);
 #pragma unroll
             for (int k = 0; k < 3; ++k) vr[k] = (e[k] > 0.f ? 1.f : (e[k] < 0.f ? -1.f : 0.f)) * (1.f / 3.f);
         } else {
-            t1 = se * (1.f / 3.f);
+            t1 += se * (1.f / 3.f);
 #pragma unroll
             for (int k = 0; k < 3; ++k) vr[k] = 2.f * e[k] * (1.f / 3.f);
         }
         const float sc = inv_count * coef;
-        float* o = v_render + pix * GSB_CH;
 #pragma unroll
         for (int k = 0; k < 3; ++k) {
-            o[k] = sc * vr[k] * ea;
-            ga += sc * vr[k] * r[k] * ea;
+            const float rk = r[k];
+            r[k] = sc * vr[k] * ea;             // the gradient replaces the pixel in shared memory
+            ga += sc * vr[k] * rk * ea;
             gb += sc * vr[k];
         }
-        o[3] = 0.f;
-        o[4] = sc * vbeta;
+        r[3] = 0.f;
+        r[4] = sc * vbeta;
+    }
+    __syncthreads();
+    {
+        float* dst = v_render + pix0 * GSB_CH;
+        if (vec) {
+            for (int i = threadIdx.x; i < 256 * GSB_CH / 4; i += 256)
+                reinterpret_cast<float4*>(dst)[i] = reinterpret_cast<const float4*>(s_r)[i];
+        } else {
+            for (int i = threadIdx.x; i < n_px * GSB_CH; i += 256) dst[i] = s_r[i];
+        }
+    }
+    __syncthreads();        // the next chunk overwrites the staging buffers
     }
     float s;
     s = block_sum_256(t1, red); if (threadIdx.x == 0 && s != 0.f) atomicAdd(loss_sum, s);
@@ -270,7 +308,8 @@ GSB_API int gsb_photo_loss(const float* render, const float* gt, const float* ex
     if (C == 0) return 0;
     GSB_CHECK_ARG(render && gt && loss_sum && v_render && C <= 65535);
     const int HW = H * W;
-    dim3 grid((HW + 255) / 256, C);
+    const int chunks = (HW + 255) / 256, per_cam = (148 * 4 + C - 1) / C;
+    dim3 grid(chunks < per_cam ? chunks : per_cam, C);
     photo_loss_kernel<<<grid, 256, 0, gsb_stream(stream)>>>(render, gt, exposure, mode, HW,
                                                             1.0f / ((float)C * (float)HW), coef, loss_sum,
                                                             loss_out, v_render, v_exposure);
@@ -282,14 +321,17 @@ GSB_API int gsb_photo_loss(const float* render, const float* gt, const float* ex
 __global__ void scale_kernel(float* __restrict__ x, int64_t n, const float* __restrict__ grad) {
     const float g = *grad;
     if (g == 1.0f) return;      // loss.backward() on the fused loss itself: nothing to do, no traffic
-    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) x[i] *= g;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) x[i] *= g;
 }
 
 GSB_API int gsb_scale_by_scalar(float* x, int64_t n, const float* grad, void* stream) {
     if (n == 0) return 0;
     GSB_CHECK_ARG(x && grad);
-    scale_kernel<<<(unsigned)((n + 255) / 256), 256, 0, gsb_stream(stream)>>>(x, n, grad);
+    // a few CTAs per SM, grid-stride: the common case (grad == 1) then costs one small launch
+    const int64_t want = (n + 255) / 256;
+    const unsigned blocks = (unsigned)(want < 148 * 8 ? want : 148 * 8);
+    scale_kernel<<<blocks, 256, 0, gsb_stream(stream)>>>(x, n, grad);
     GSB_LAUNCH_CHECK();
     return 0;
 }
