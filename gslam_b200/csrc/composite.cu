@@ -16,7 +16,9 @@
 // warps are slower at every setting (12/16/20/24 per SM: 90/83/81/82 us against 78), and two-warp
 // CTAs squeezed to 56 registers to make all 4800 units of a 640x480 view resident spill and lose
 // more than the missing second wave gains.
+#ifndef PPT
 #define PPT 2
+#endif
 #define CMP_WARPS 1
 #include "composite.cuh"
 #ifdef GSB_TRACE

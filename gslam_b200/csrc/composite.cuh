@@ -36,18 +36,25 @@
 #ifndef PPT
 #define PPT 2                  // pixels per thread: 2 -> 8x8 quarter-tile units, 4 -> 16x8 half-tiles
 #endif
-#if PPT == 2
+#if PPT == 1
+#define UNITS_PER_TILE 8
+#define UNIT_W 8
+#define UNIT_H 4
+#define SLOT_DX(j) 0
+#define SLOT_DY(j) 0
+#elif PPT == 2
 #define UNITS_PER_TILE 4
 #define UNIT_W 8
+#define UNIT_H 8
 #define SLOT_DX(j) 0
 #define SLOT_DY(j) ((j) * 4)
 #else
 #define UNITS_PER_TILE 2
 #define UNIT_W 16
+#define UNIT_H 8
 #define SLOT_DX(j) (((j) & 1) * 8)
 #define SLOT_DY(j) (((j) >> 1) * 4)
 #endif
-#define UNIT_H 8
 
 struct TileRange {
     int start, end;
@@ -156,8 +163,8 @@ __device__ __forceinline__ Unit decode_unit(int unit, int lane, int tile_w, int 
     u.cam = u.lin / n_tiles;
     const int tile = u.lin - u.cam * n_tiles;
     const int ty = tile / tile_w, tx = tile - ty * tile_w;
-    const int ox = tx * GSB_TILE + (UNITS_PER_TILE == 4 ? (q & 1) * 8 : 0);
-    const int oy = ty * GSB_TILE + (UNITS_PER_TILE == 4 ? (q >> 1) * 8 : q * 8);
+    const int ox = tx * GSB_TILE + (UNITS_PER_TILE >= 4 ? (q & 1) * 8 : 0);
+    const int oy = ty * GSB_TILE + (UNITS_PER_TILE >= 4 ? (q >> 1) * UNIT_H : q * 8);
     u.bx = ox + (lane & 7);
     u.by = oy + (lane >> 3);
     u.rc.x0 = (float)ox + 0.5f; u.rc.x1 = u.rc.x0 + (float)(UNIT_W - 1);

@@ -200,6 +200,16 @@ int gsb_adam_multi(const gsb_adam_tensor* tensors_host, int n_tensors, float bet
                    float eps, int step, int decay_tensor, const int32_t* vis_count, int vis_div,
                    float decay, int32_t* step_dev, void* stream);
 
+/* ---- K11: camera pose chain -------------------------------------------------------------
+ * Replaces PoseZhou.forward + rotation_6d_to_matrix, reference gslam/primitives.py:15-36, 82-92
+ * (batched over the views that gslam/map.py:57,86 stacks with create_batch):
+ *   viewmats[c] = Rt[c] . [[GS(dR[c] + (1,0,0,0,1,0)), dt[c]], [0 0 0 1]]
+ * Rt [C,4,4], dR [C,6], dt [C,3], viewmats [C,4,4], row-major f32.  gsb_pose_bwd is its gradient:
+ * v_viewmats [C,4,4] -> v_dR [C,6], v_dt [C,3] (either output may be NULL). */
+int gsb_pose_fwd(const float* Rt, const float* dR, const float* dt, int C, float* viewmats, void* stream);
+int gsb_pose_bwd(const float* Rt, const float* dR, const float* v_viewmats, int C, float* v_dR,
+                 float* v_dt, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
