@@ -28,7 +28,8 @@ SIGNATURES = {
     "gsb_version": (_i, []),
     "gsb_last_error": (ct.c_char_p, []),
     "gsb_read_i64_host": (_i, [_p, _p, _p]),
-    "gsb_project_fwd": (_i, [_p] * 8 + [_i, _i, _i, _i, _f, _f, _f, _f, _i, _i] + [_p] * 5 + [_p]),
+    "gsb_project_fwd": (_i, [_p] * 8 + [_i, _i, _i, _i, _f, _f, _f, _f, _i, _i] + [_p] * 5 + [_p, _i, _i] + [_p]),
+    "gsb_sh_bwd": (_i, [_p, _p, _i, _i, _p, _p, _p, _i, _i, _p, _p, _p]),
     "gsb_tile_scan": (_i, [_p, _i, _i, _i, _p, _p, _p, _p]),
     "gsb_isect_scatter": (_i, [_p, _p, _p, _i, _i, _i, _i, _p, _l, _p, _p, _p]),
     "gsb_segment_sort": (_i, [_p, _p, _p, _i, _i, _i, _i, _l, _p, _p, _p]),

@@ -6,6 +6,7 @@
 // gradients accumulate in registers over cameras (no atomics), and only the
 // per-camera pose gradient needs a block reduction.
 #include "common.cuh"
+#include "sh.cuh"
 
 #define MAX_CAMS_SMEM 64
 
@@ -138,7 +139,8 @@ project_fwd_kernel(const float* __restrict__ means, const float* __restrict__ qu
                    int width, int height, float eps2d, float near_plane, float far_plane,
                    float radius_clip, int tile_w, int tile_h, int32_t* __restrict__ radii,
                    float* __restrict__ means2d, float* __restrict__ rec,
-                   int32_t* __restrict__ tiles_per_gauss, int32_t* __restrict__ tile_counts) {
+                   int32_t* __restrict__ tiles_per_gauss, int32_t* __restrict__ tile_counts,
+                   const float* __restrict__ sh_coeffs, int sh_degree, int sh_stride) {
     __shared__ Cam cams[MAX_CAMS_SMEM];
     int n = blockIdx.x * blockDim.x + threadIdx.x;
     float mu[3], q[4], ls[3], Rq[9], s[3], Sig[9], qinv;
@@ -150,9 +152,11 @@ project_fwd_kernel(const float* __restrict__ means, const float* __restrict__ qu
         ls[0] = log_scales[n * 3]; ls[1] = log_scales[n * 3 + 1]; ls[2] = log_scales[n * 3 + 2];
         build_sigma(q, ls, Rq, s, Sig, qinv);
         opac = sigmoidf_(logit_opac[n]);
-        col[0] = sigmoidf_(logit_colors[n * 3]);
-        col[1] = sigmoidf_(logit_colors[n * 3 + 1]);
-        col[2] = sigmoidf_(logit_colors[n * 3 + 2]);
+        if (!sh_coeffs) {
+            col[0] = sigmoidf_(logit_colors[n * 3]);
+            col[1] = sigmoidf_(logit_colors[n * 3 + 1]);
+            col[2] = sigmoidf_(logit_colors[n * 3 + 2]);
+        }
         if (log_unc) beta = fmaxf(expf(log_unc[n]), 0.01f);
     }
     for (int c0 = 0; c0 < C; c0 += MAX_CAMS_SMEM) {
@@ -170,6 +174,11 @@ project_fwd_kernel(const float* __restrict__ means, const float* __restrict__ qu
             int rad = 0, cnt = 0, x0 = 0, x1 = 0, y0 = 0, y1 = 0;
             float2 m2 = make_float2(0.f, 0.f);
             if (p.ok) {
+                if (sh_coeffs) {    // view-dependent colour (extension; the reference path is the sigmoid above)
+                    float centre[3];
+                    cam_centre(cams[ci].R, cams[ci].t, centre);
+                    sh_colour(sh_degree, sh_coeffs + (size_t)n * sh_stride * 3, sh_num_coeffs(sh_degree), mu, centre, col);
+                }
                 float idet = 1.0f / p.det;
                 rad = (int)p.radius;
                 m2 = make_float2(p.mx, p.my);
@@ -202,16 +211,19 @@ GSB_API int gsb_project_fwd(const float* means, const float* quats, const float*
                             int N, int width, int height, float eps2d, float near_plane,
                             float far_plane, float radius_clip, int tile_w, int tile_h,
                             int32_t* radii, float* means2d, float* rec, int32_t* tiles_per_gauss,
-                            int32_t* tile_counts, void* stream) {
+                            int32_t* tile_counts, const float* sh_coeffs, int sh_degree, int sh_stride,
+                            void* stream) {
     GSB_CHECK_ARG(C >= 0 && N >= 0 && width > 0 && height > 0);
     if (C == 0 || N == 0) return 0;
-    GSB_CHECK_ARG(means && quats && log_scales && logit_opacities && logit_colors && viewmats && Ks);
+    GSB_CHECK_ARG(means && quats && log_scales && logit_opacities && viewmats && Ks);
+    GSB_CHECK_ARG(logit_colors || sh_coeffs);
+    GSB_CHECK_ARG(!sh_coeffs || (sh_degree >= 0 && sh_degree <= 3 && sh_stride >= (sh_degree + 1) * (sh_degree + 1)));
     GSB_CHECK_ARG(radii && means2d && rec && tiles_per_gauss);
     int blocks = (N + 255) / 256;
     project_fwd_kernel<<<blocks, 256, 0, gsb_stream(stream)>>>(
         means, quats, log_scales, logit_opacities, logit_colors, log_unc, viewmats, Ks, C, N, width,
         height, eps2d, near_plane, far_plane, radius_clip, tile_w, tile_h, radii, means2d, rec,
-        tiles_per_gauss, tile_counts);
+        tiles_per_gauss, tile_counts, sh_coeffs, sh_degree, sh_stride);
     GSB_LAUNCH_CHECK();
     return 0;
 }
@@ -395,10 +407,12 @@ project_bwd_kernel(const float* __restrict__ means, const float* __restrict__ qu
     v_log_scales[n * 3] = v_ls[0]; v_log_scales[n * 3 + 1] = v_ls[1]; v_log_scales[n * 3 + 2] = v_ls[2];
     float o = sigmoidf_(logit_opac[n]);
     v_logit_opac[n] = v_opac * o * (1.f - o);
+    if (logit_colors) {     // NULL with SH colours: gsb_sh_bwd owns that gradient
 #pragma unroll
-    for (int k = 0; k < 3; ++k) {
-        float cc = sigmoidf_(logit_colors[n * 3 + k]);
-        v_logit_colors[n * 3 + k] = v_col[k] * cc * (1.f - cc);
+        for (int k = 0; k < 3; ++k) {
+            float cc = sigmoidf_(logit_colors[n * 3 + k]);
+            v_logit_colors[n * 3 + k] = v_col[k] * cc * (1.f - cc);
+        }
     }
     if (log_unc && v_log_unc) {
         float bexp = expf(log_unc[n]);
@@ -417,10 +431,10 @@ GSB_API int gsb_project_bwd(const float* means, const float* quats, const float*
     (void)rec;
     GSB_CHECK_ARG(C >= 0 && N >= 0);
     if (C == 0 || N == 0) return 0;
-    GSB_CHECK_ARG(means && quats && log_scales && logit_opacities && logit_colors && viewmats && Ks);
+    GSB_CHECK_ARG(means && quats && log_scales && logit_opacities && viewmats && Ks);
     GSB_CHECK_ARG(radii && v_means2d && v_rec && v_means2d_stride >= 2);
-    if (need_gauss_grads)
-        GSB_CHECK_ARG(v_means && v_quats && v_log_scales && v_logit_opacities && v_logit_colors);
+    if (need_gauss_grads)   // logit_colors == NULL: SH colours, their gradient comes from gsb_sh_bwd
+        GSB_CHECK_ARG(v_means && v_quats && v_log_scales && v_logit_opacities && (v_logit_colors || !logit_colors));
     int blocks = (N + 255) / 256;
     project_bwd_kernel<<<blocks, 256, 0, gsb_stream(stream)>>>(
         means, quats, log_scales, logit_opacities, logit_colors, log_unc, viewmats, Ks, C, N, width,

@@ -44,7 +44,10 @@ def tile_bits(tile_w: int, tile_h: int, n_cameras: int):
 class _Project(torch.autograd.Function):
     @staticmethod
     def forward(ctx, means, quats, log_scales, logit_opacities, logit_colors, log_unc, viewmats, Ks,
-                width, height, eps2d, near_plane, far_plane, radius_clip, tile_w, tile_h, tile_counts):
+                width, height, eps2d, near_plane, far_plane, radius_clip, tile_w, tile_h, tile_counts,
+                sh_degree=None):
+        """sh_degree None: logit_colors [N,3] -> sigmoid (the reference).  sh_degree 0..3 (extension):
+        logit_colors holds SH coefficients [N,K,3], K >= (sh_degree+1)^2."""
         ctx.set_materialize_grads(False)    # no zero-fill kernels for the integer outputs' "gradients"
         means, quats, log_scales = _c(means), _c(quats), _c(log_scales)
         logit_opacities, logit_colors, log_unc = _c(logit_opacities), _c(logit_colors), _c(log_unc)
@@ -57,11 +60,21 @@ class _Project(torch.autograd.Function):
         rec = torch.empty(C, N, REC, dtype=torch.float32, device=dev)
         if tile_counts is None:
             tile_counts = torch.zeros(C, tile_h * tile_w, CSTRIDE, dtype=torch.int32, device=dev)
-        call("gsb_project_fwd", 
-            ptr(means), ptr(quats), ptr(log_scales), ptr(logit_opacities), ptr(logit_colors),
+        sh = sh_degree is not None
+        if sh:
+            if not (0 <= sh_degree <= 3):
+                raise NotImplementedError("sh_degree must be 0..3")
+            if logit_colors.dim() != 3 or logit_colors.shape[2] != 3 or \
+                    logit_colors.shape[1] < (sh_degree + 1) ** 2:
+                raise ValueError("with sh_degree set, logit_colors must be [N, K >= (sh_degree+1)^2, 3]")
+        call("gsb_project_fwd",
+            ptr(means), ptr(quats), ptr(log_scales), ptr(logit_opacities),
+            None if sh else ptr(logit_colors),
             ptr(log_unc), ptr(viewmats), ptr(Ks), C, N, width, height, eps2d, near_plane, far_plane,
             radius_clip, tile_w, tile_h, ptr(radii), ptr(means2d), ptr(rec), ptr(tiles),
-            ptr(tile_counts), stream())
+            ptr(tile_counts), ptr(logit_colors) if sh else None, sh_degree if sh else -1,
+            logit_colors.shape[1] if sh else 0, stream())
+        ctx.sh_degree = sh_degree
         ctx.save_for_backward(means, quats, log_scales, logit_opacities, logit_colors, log_unc,
                               viewmats, Ks, radii, rec)
         ctx.dims = (C, N, width, height, eps2d)
@@ -103,16 +116,22 @@ class _Project(torch.autograd.Function):
         else:
             v_means = v_quats = v_scales = v_opac = v_colors = v_unc = None
         v_view = torch.zeros(C, 4, 4, dtype=torch.float32, device=dev) if need_view else None
+        sh = ctx.sh_degree is not None
         if need_gauss or need_view:
-            call("gsb_project_bwd", 
-                ptr(means), ptr(quats), ptr(log_scales), ptr(logit_opacities), ptr(logit_colors),
+            call("gsb_project_bwd",
+                ptr(means), ptr(quats), ptr(log_scales), ptr(logit_opacities),
+                None if sh else ptr(logit_colors),
                 ptr(log_unc), ptr(viewmats), ptr(Ks), C, N, width, height, eps2d, ptr(radii), ptr(rec),
                 ptr(g_means2d), m2_stride, ptr(g_rec), int(need_gauss), ptr(v_means), ptr(v_quats),
-                ptr(v_scales), ptr(v_opac), ptr(v_colors), ptr(v_unc), ptr(v_view), stream())
+                ptr(v_scales), ptr(v_opac), None if sh else ptr(v_colors), ptr(v_unc), ptr(v_view), stream())
+        if sh and need_gauss:
+            v_colors = torch.empty_like(logit_colors)
+            call("gsb_sh_bwd", ptr(means), ptr(logit_colors), ctx.sh_degree, logit_colors.shape[1],
+                 ptr(viewmats), ptr(radii), ptr(g_rec), C, N, ptr(v_colors), ptr(v_means), stream())
         grads = [v_means, v_quats, v_scales, v_opac, v_colors,
                  v_unc if log_unc is not None else None]
         grads = [g if n else None for g, n in zip(grads, need[:6])]
-        return (*grads, v_view, None, None, None, None, None, None, None, None, None, None)
+        return (*grads, v_view, None, None, None, None, None, None, None, None, None, None, None)
 
 
 class _Composite(torch.autograd.Function):
@@ -166,12 +185,13 @@ class _Composite(torch.autograd.Function):
 
 
 def project(means, quats, log_scales, logit_opacities, logit_colors, log_unc, viewmats, Ks, width,
-            height, eps2d=0.3, near_plane=0.01, far_plane=1e10, radius_clip=0.0, tile_counts=None):
+            height, eps2d=0.3, near_plane=0.01, far_plane=1e10, radius_clip=0.0, tile_counts=None,
+            sh_degree=None):
     """tile_counts: optional pre-zeroed int32 [C, T, 32] (see ZeroPool)."""
     tile_w, tile_h = math.ceil(width / TILE), math.ceil(height / TILE)
     return _Project.apply(means, quats, log_scales, logit_opacities, logit_colors, log_unc, viewmats,
                           Ks, int(width), int(height), float(eps2d), float(near_plane),
-                          float(far_plane), float(radius_clip), tile_w, tile_h, tile_counts)
+                          float(far_plane), float(radius_clip), tile_w, tile_h, tile_counts, sh_degree)
 
 
 class ZeroPool:

@@ -93,9 +93,16 @@ def rasterization(
     log_uncertainties: Optional[Tensor] = None,
     visibility_min_T: float = 0.5,
     mask: Optional[Tensor] = None,
+    sh_degree: Optional[int] = None,
 ) -> RasterizationOutput:
     """Rasterize N Gaussians to C image planes; see the reference docstring
-    (gslam/rasterization.py:72-119) for the argument meanings."""
+    (gslam/rasterization.py:72-119) for the argument meanings.
+
+    ``sh_degree`` is the one extension beyond the reference surface (SURVEY 8a "SH note", BASELINE
+    cfg4): None keeps the reference's ``sigmoid(logit_colors)``; 0..3 reads ``logit_colors`` as real
+    spherical-harmonics coefficients ``[N, K >= (sh_degree+1)^2, 3]`` and colours each (view,
+    Gaussian) pair ``max(SH(normalize(mean - camera centre)) + 0.5, 0)``, gradients to the
+    coefficients and to the means."""
     N = means.shape[0]
     C = viewmats.shape[0]
     assert means.shape == (N, 3), means.shape
@@ -117,8 +124,8 @@ def rasterization(
         _unsupported("sparse_grad / absgrad")
     if rasterize_mode != "classic" or camera_model != "pinhole":
         _unsupported("rasterize_mode / camera_model other than classic / pinhole")
-    if logit_colors.dim() != 2 or logit_colors.shape != (N, 3):
-        _unsupported(f"logit_colors of shape {tuple(logit_colors.shape)} (only [N,3])")
+    if sh_degree is None and (logit_colors.dim() != 2 or logit_colors.shape != (N, 3)):
+        _unsupported(f"logit_colors of shape {tuple(logit_colors.shape)} (only [N,3] without sh_degree)")
     if not means.is_cuda:
         raise RuntimeError("gslam_b200.rasterization needs CUDA tensors; there is no CPU path")
 
@@ -130,7 +137,8 @@ def rasterization(
     # K8+K1 (+ tile counting): activations, projection and record packing in one kernel
     radii, means2d, rec, tiles_per_gauss, tile_counts = ops.project(
         means, quats, log_scales, logit_opacities, logit_colors, log_uncertainties, viewmats, Ks,
-        width, height, eps2d, near_plane, far_plane, radius_clip, tile_counts=zeros.tile_counts)
+        width, height, eps2d, near_plane, far_plane, radius_clip, tile_counts=zeros.tile_counts,
+        sh_degree=sh_degree)
 
     # K4+K5: counting sort by tile + per-tile depth sort (bit-identical to the upstream
     # emit / stable radix sort / offset-encode chain, which ops.isect_tiles still provides)

@@ -51,14 +51,19 @@ int gsb_read_i64_host(const int64_t* src, int64_t* dst_host, void* stream);
  * Outputs: radii[C,N] i32, means2d[C,N,2], rec[C,N,12], tiles_per_gauss[C,N] i32.
  * tile_counts[C*tile_h*tile_w*GSB_CSTRIDE] i32 (may be NULL; zeroed by the caller) receives
  * at index i*GSB_CSTRIDE the
- * number of intersections per (camera, tile) for the tile-binned sort below. */
+ * number of intersections per (camera, tile) for the tile-binned sort below.
+ * View-dependent colours (extension, SURVEY 8a "SH note"; the reference has none): when sh_coeffs
+ * [N, sh_stride, 3] is not NULL the record colour is max(SH_deg(d) + 0.5, 0) with
+ * d = normalize(mean - camera centre), real SH basis of degree sh_degree <= 3 over the first
+ * (sh_degree+1)^2 coefficients, and logit_colors may be NULL. */
 int gsb_project_fwd(const float* means, const float* quats, const float* log_scales,
                     const float* logit_opacities, const float* logit_colors,
                     const float* log_unc, const float* viewmats, const float* Ks,
                     int C, int N, int width, int height, float eps2d, float near_plane,
                     float far_plane, float radius_clip, int tile_w, int tile_h,
                     int32_t* radii, float* means2d, float* rec, int32_t* tiles_per_gauss,
-                    int32_t* tile_counts, void* stream);
+                    int32_t* tile_counts, const float* sh_coeffs, int sh_degree, int sh_stride,
+                    void* stream);
 
 /* K2+K8 backward.  v_rec[C,N,12] carries the gradients of every record slot
  * except x,y, which come from v_means2d (element stride `v_means2d_stride`
@@ -66,7 +71,8 @@ int gsb_project_fwd(const float* means, const float* quats, const float* log_sca
  * Outputs (overwritten, summed over cameras): v_means[N,3] v_quats[N,4]
  * v_log_scales[N,3] v_logit_opacities[N] v_logit_colors[N,3] v_log_unc[N]
  * (any may be NULL when need_gauss_grads == 0) and v_viewmats[C,4,4] (must be
- * zeroed by the caller; accumulated atomically; may be NULL). */
+ * zeroed by the caller; accumulated atomically; may be NULL).  With SH colours pass
+ * logit_colors = v_logit_colors = NULL and call gsb_sh_bwd afterwards. */
 int gsb_project_bwd(const float* means, const float* quats, const float* log_scales,
                     const float* logit_opacities, const float* logit_colors,
                     const float* log_unc, const float* viewmats, const float* Ks,
@@ -77,6 +83,13 @@ int gsb_project_bwd(const float* means, const float* quats, const float* log_sca
                     float* v_means, float* v_quats, float* v_log_scales,
                     float* v_logit_opacities, float* v_logit_colors, float* v_log_unc,
                     float* v_viewmats, void* stream);
+
+/* Backward of the SH colours of gsb_project_fwd: v_sh[N, sh_stride, 3] is overwritten (summed over
+ * cameras), the view-direction term is ADDED to v_means[N,3] (may be NULL), so call it after
+ * gsb_project_bwd on the same stream.  The camera centre is treated as a constant. */
+int gsb_sh_bwd(const float* means, const float* sh_coeffs, int sh_degree, int sh_stride,
+               const float* viewmats, const int32_t* radii, const float* v_rec, int C, int N,
+               float* v_sh, float* v_means, void* stream);
 
 /* K3: packed projection (reference gslam/rasterization.py:390-419).  Two calls:
  * gsb_project_fwd (unpacked) then gsb_pack_visible compacts the rows with

@@ -58,6 +58,42 @@ def activations(log_scales, logit_opacities, logit_colors, log_uncertainties=Non
 
 
 # ----------------------------------------------------------------------------
+# Spherical-harmonics colours: EXTENSION (SURVEY 8a "SH note"); the reference has none.
+# Published algorithm restated: real SH basis to degree 3 in the 3DGS / gsplat sign convention,
+# colour = clamp_min(sum_k Y_k(d) c_k + 0.5, 0), d = normalize(mean - camera centre), the camera
+# centre taken as a constant.  Written as explicit polynomials, independent of the kernel's code.
+# ----------------------------------------------------------------------------
+def sh_basis(degree: int, dirs: Tensor) -> Tensor:
+    """dirs [..., 3] unit vectors -> [..., (degree+1)^2]."""
+    x, y, z = dirs.unbind(-1)
+    Y = [torch.full_like(x, 0.28209479177387814)]
+    if degree >= 1:
+        c1 = 0.4886025119029199
+        Y += [-c1 * y, c1 * z, -c1 * x]
+    if degree >= 2:
+        Y += [1.0925484305920792 * x * y, -1.0925484305920792 * y * z,
+              0.31539156525252005 * (2 * z * z - x * x - y * y),
+              -1.0925484305920792 * x * z, 0.5462742152960396 * (x * x - y * y)]
+    if degree >= 3:
+        Y += [-0.5900435899266435 * y * (3 * x * x - y * y), 2.890611442640554 * x * y * z,
+              -0.4570457994644658 * y * (4 * z * z - x * x - y * y),
+              0.3731763325901154 * z * (2 * z * z - 3 * x * x - 3 * y * y),
+              -0.4570457994644658 * x * (4 * z * z - x * x - y * y),
+              1.445305721320277 * z * (x * x - y * y), -0.5900435899266435 * x * (x * x - 3 * y * y)]
+    return torch.stack(Y, dim=-1)
+
+
+def sh_colors(degree: int, coeffs: Tensor, means: Tensor, viewmats: Tensor) -> Tensor:
+    """coeffs [N,K,3], means [N,3], viewmats [C,4,4] -> colours [C,N,3]."""
+    K = (degree + 1) ** 2
+    Rm, t = viewmats[:, :3, :3].detach(), viewmats[:, :3, 3].detach()
+    centre = -(Rm.transpose(1, 2) @ t[..., None])[..., 0]                  # [C,3]
+    dirs = F.normalize(means[None] - centre[:, None], dim=-1)               # [C,N,3]
+    Y = sh_basis(degree, dirs)                                              # [C,N,K]
+    return ((Y[..., None] * coeffs[None, :, :K, :]).sum(-2) + 0.5).clamp_min(0.0)
+
+
+# ----------------------------------------------------------------------------
 # quaternion (wxyz, not necessarily unit) + scale -> covariance
 # (gsplat.quat_scale_to_covar_preci; reference call gslam/insertion.py:88)
 # ----------------------------------------------------------------------------
@@ -383,7 +419,7 @@ def rasterization(
     means, quats, log_scales, logit_opacities, logit_colors, viewmats, Ks, width, height,
     near_plane=0.01, far_plane=1e10, radius_clip=0.0, eps2d=0.3, packed=False, tile_size=16,
     backgrounds=None, render_mode="RGB", log_uncertainties=None, visibility_min_T=0.5,
-    return_stats=False,
+    return_stats=False, sh_degree=None,
 ):
     """Unpacked path of reference gslam/rasterization.py:44-360 (the only one
     its callers use, gslam/map.py:59-74, 88-103)."""
@@ -395,7 +431,10 @@ def rasterization(
     radii, means2d, depths, conics = fully_fused_projection(
         means, quats, scales, viewmats, Ks, width, height, eps2d, near_plane, far_plane, radius_clip)
     opacities = opacities.repeat(C, 1)                                    # :187
-    colors = colors.expand(C, -1, -1)                                     # :225
+    if sh_degree is None:
+        colors = colors.expand(C, -1, -1)                                 # :225
+    else:                                                                 # extension, see sh_colors
+        colors = sh_colors(sh_degree, logit_colors, means, viewmats)
     depth_index = betas_index = None
     if render_mode == "RGB+D":
         colors = torch.cat((colors, depths[..., None]), dim=-1)           # :235

@@ -29,12 +29,12 @@ def test_bad_arguments_return_codes_not_crashes():
     L = _lib.lib()
     # width <= 0 -> GSB_EINVAL before any CUDA call
     rc = L.gsb_project_fwd(None, None, None, None, None, None, None, None, 1, 1, 0, 0,
-                           0.3, 0.01, 1e10, 0.0, 1, 1, None, None, None, None, None, None)
+                           0.3, 0.01, 1e10, 0.0, 1, 1, None, None, None, None, None, None, -1, 0, None)
     assert rc == -1
     assert b"bad argument" in L.gsb_last_error()
     # empty problems are a no-op success
     assert L.gsb_project_fwd(None, None, None, None, None, None, None, None, 0, 0, 8, 8,
-                             0.3, 0.01, 1e10, 0.0, 1, 1, None, None, None, None, None, None) == 0
+                             0.3, 0.01, 1e10, 0.0, 1, 1, None, None, None, None, None, None, -1, 0, None) == 0
 
 
 def test_no_oracle_import_in_product():

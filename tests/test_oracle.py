@@ -235,3 +235,23 @@ def test_quat_scale_to_covar_preci_shim_matches_oracle():
     covar, preci = quat_scale_to_covar_preci(q, s)
     assert torch.allclose(covar, R.quat_scale_to_covar(q, s), atol=1e-6)
     assert torch.allclose(covar @ preci, torch.eye(3).expand(64, 3, 3), atol=1e-4)
+
+
+def test_sh_basis_is_orthonormal_and_degree0_constant():
+    """SH extension of the oracle: the 16 basis functions are orthonormal on the sphere
+    (Monte-Carlo quadrature), and a degree-0 colour does not depend on the view."""
+    g = torch.Generator().manual_seed(0)
+    d = torch.nn.functional.normalize(torch.randn(400_000, 3, generator=g, dtype=torch.float64), dim=-1)
+    Y = R.sh_basis(3, d)
+    gram = (Y.T @ Y) * (4 * math.pi / d.shape[0])
+    assert torch.allclose(gram, torch.eye(16, dtype=torch.float64), atol=2e-2)
+    means = torch.randn(50, 3, generator=g)
+    vm = torch.eye(4).repeat(3, 1, 1)
+    vm[1, :3, 3] = torch.tensor([0.3, -0.2, 0.5])
+    vm[2, :3, 3] = torch.tensor([-1.0, 0.4, 0.1])
+    c = torch.randn(50, 16, 3, generator=g)
+    col0 = R.sh_colors(0, c, means, vm)
+    assert torch.allclose(col0[0], col0[1]) and torch.allclose(col0[0], col0[2])
+    col3 = R.sh_colors(3, c, means, vm)
+    assert not torch.allclose(col3[0], col3[2])
+    assert float(col3.min()) >= 0.0
