@@ -15,10 +15,28 @@ sh_bwd_kernel(const float* __restrict__ means, const float* __restrict__ coeffs,
     const float mu[3] = {means[n * 3], means[n * 3 + 1], means[n * 3 + 2]};
     const float* cf = coeffs + (size_t)n * sh_stride * 3;
     float c[K][3], vc[K][3];
+    // 16-byte accesses when the row allows it (K = 4, 16 with a matching stride): see sh_colour
+    const bool vec = (K * 3) % 4 == 0 && (sh_stride * 3) % 4 == 0 &&
+                     ((reinterpret_cast<uintptr_t>(coeffs) | reinterpret_cast<uintptr_t>(v_sh)) & 15) == 0;
+    if (vec) {
+        const float4* c4 = reinterpret_cast<const float4*>(cf);
+#pragma unroll
+        for (int v = 0; v < K * 3 / 4; ++v) {
+            const float4 q = c4[v];
+            const float e[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+            for (int j = 0; j < 4; ++j) c[(v * 4 + j) / 3][(v * 4 + j) % 3] = e[j];
+        }
+    } else {
+#pragma unroll
+        for (int k = 0; k < K; ++k)
+#pragma unroll
+            for (int ch = 0; ch < 3; ++ch) c[k][ch] = cf[k * 3 + ch];
+    }
 #pragma unroll
     for (int k = 0; k < K; ++k)
 #pragma unroll
-        for (int ch = 0; ch < 3; ++ch) { c[k][ch] = cf[k * 3 + ch]; vc[k][ch] = 0.f; }
+        for (int ch = 0; ch < 3; ++ch) vc[k][ch] = 0.f;
     float vmu[3] = {0.f, 0.f, 0.f};
     for (int cam = 0; cam < C; ++cam) {
         const size_t idx = (size_t)cam * N + n;
@@ -59,10 +77,18 @@ sh_bwd_kernel(const float* __restrict__ means, const float* __restrict__ coeffs,
         vmu[2] += (gz - dotp * z) * inv;
     }
     float* out = v_sh + (size_t)n * sh_stride * 3;
+    if (vec) {
+        float4* o4 = reinterpret_cast<float4*>(out);
 #pragma unroll
-    for (int k = 0; k < K; ++k)
+        for (int v = 0; v < K * 3 / 4; ++v)
+            o4[v] = make_float4(vc[(v * 4) / 3][(v * 4) % 3], vc[(v * 4 + 1) / 3][(v * 4 + 1) % 3],
+                                vc[(v * 4 + 2) / 3][(v * 4 + 2) % 3], vc[(v * 4 + 3) / 3][(v * 4 + 3) % 3]);
+    } else {
 #pragma unroll
-        for (int ch = 0; ch < 3; ++ch) out[k * 3 + ch] = vc[k][ch];
+        for (int k = 0; k < K; ++k)
+#pragma unroll
+            for (int ch = 0; ch < 3; ++ch) out[k * 3 + ch] = vc[k][ch];
+    }
     for (int k = K; k < sh_stride; ++k)      // coefficients above the active degree get no gradient
         for (int ch = 0; ch < 3; ++ch) out[k * 3 + ch] = 0.f;
     if (v_means) {
