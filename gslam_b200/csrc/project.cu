@@ -30,6 +30,18 @@ __device__ __forceinline__ void load_cams(Cam* cams, const float* viewmats, cons
     }
 }
 
+// Row n of a [N,4] tensor.  One 16-byte access when the base allows it: as views of a flat [15 N]
+// buffer (mapping.FlatSplats, the flat gradient of project_bwd) the quaternion rows start 12 N bytes
+// in, which is 16-byte aligned only when N is a multiple of 4.
+__device__ __forceinline__ float4 load_row4(const float* base, int n) {
+    if ((reinterpret_cast<uintptr_t>(base) & 15) == 0) return reinterpret_cast<const float4*>(base)[n];
+    return make_float4(base[n * 4], base[n * 4 + 1], base[n * 4 + 2], base[n * 4 + 3]);
+}
+__device__ __forceinline__ void store_row4(float* base, int n, float4 v) {
+    if ((reinterpret_cast<uintptr_t>(base) & 15) == 0) { reinterpret_cast<float4*>(base)[n] = v; return; }
+    base[n * 4] = v.x; base[n * 4 + 1] = v.y; base[n * 4 + 2] = v.z; base[n * 4 + 3] = v.w;
+}
+
 // Rotation of the normalised quaternion (wxyz), row-major.
 __device__ __forceinline__ void quat_to_R(float w, float x, float y, float z, float* R) {
     R[0] = 1.f - 2.f * (y * y + z * z); R[1] = 2.f * (x * y - w * z); R[2] = 2.f * (x * z + w * y);
@@ -147,7 +159,7 @@ project_fwd_kernel(const float* __restrict__ means, const float* __restrict__ qu
     float opac = 0.f, col[3] = {0.f, 0.f, 0.f}, beta = 0.f;
     if (n < N) {
         mu[0] = means[n * 3]; mu[1] = means[n * 3 + 1]; mu[2] = means[n * 3 + 2];
-        float4 qq = reinterpret_cast<const float4*>(quats)[n];
+        float4 qq = load_row4(quats, n);
         q[0] = qq.x; q[1] = qq.y; q[2] = qq.z; q[3] = qq.w;
         ls[0] = log_scales[n * 3]; ls[1] = log_scales[n * 3 + 1]; ls[2] = log_scales[n * 3 + 2];
         build_sigma(q, ls, Rq, s, Sig, qinv);
@@ -251,7 +263,7 @@ project_bwd_kernel(const float* __restrict__ means, const float* __restrict__ qu
     float mu[3] = {0.f, 0.f, 0.f}, q[4], ls[3], Rq[9], s[3], Sig[9], qinv = 1.f;
     if (n < N) {
         mu[0] = means[n * 3]; mu[1] = means[n * 3 + 1]; mu[2] = means[n * 3 + 2];
-        float4 qq = reinterpret_cast<const float4*>(quats)[n];
+        float4 qq = load_row4(quats, n);
         q[0] = qq.x; q[1] = qq.y; q[2] = qq.z; q[3] = qq.w;
         ls[0] = log_scales[n * 3]; ls[1] = log_scales[n * 3 + 1]; ls[2] = log_scales[n * 3 + 2];
         build_sigma(q, ls, Rq, s, Sig, qinv);
@@ -403,7 +415,7 @@ project_bwd_kernel(const float* __restrict__ means, const float* __restrict__ qu
     float4 vq = make_float4((vqn[0] - dotp * w) * qinv, (vqn[1] - dotp * x) * qinv,
                             (vqn[2] - dotp * y) * qinv, (vqn[3] - dotp * z) * qinv);
     v_means[n * 3] = v_mu[0]; v_means[n * 3 + 1] = v_mu[1]; v_means[n * 3 + 2] = v_mu[2];
-    reinterpret_cast<float4*>(v_quats)[n] = vq;
+    store_row4(v_quats, n, vq);
     v_log_scales[n * 3] = v_ls[0]; v_log_scales[n * 3 + 1] = v_ls[1]; v_log_scales[n * 3 + 2] = v_ls[2];
     float o = sigmoidf_(logit_opac[n]);
     v_logit_opac[n] = v_opac * o * (1.f - o);

@@ -213,6 +213,21 @@ int gsb_adam_multi(const gsb_adam_tensor* tensors_host, int n_tensors, float bet
                    float eps, int step, int decay_tensor, const int32_t* vis_count, int vis_div,
                    float decay, int32_t* step_dev, void* stream);
 
+/* ---- densify / prune surgery ------------------------------------------------
+ * Replaces the per-tensor `value[keep_mask]` / `torch.cat` loops of gslam/pruning.py:10-53 and
+ * gslam/insertion.py:27-62 over the 6 parameters and their 12 Adam states: every listed tensor
+ * [n_old, width] is compacted to the rows kept by the mask (keep_cum = inclusive int64 scan of the
+ * mask, NULL = keep all; n_keep = its last element) and n_add rows are appended from `add`
+ * (NULL = zeros, i.e. fresh optimizer state).  dst has n_keep + n_add rows and must not alias src. */
+typedef struct {
+    const float* src;
+    float* dst;
+    const float* add;
+    int width;
+} gsb_row_tensor;
+int gsb_rows_resize(const gsb_row_tensor* tensors_host, int n_tensors, int64_t n_old,
+                    const int64_t* keep_cum, int64_t n_keep, int64_t n_add, void* stream);
+
 /* ---- K11: camera pose chain -------------------------------------------------------------
  * Replaces PoseZhou.forward + rotation_6d_to_matrix, reference gslam/primitives.py:15-36, 82-92
  * (batched over the views that gslam/map.py:57,86 stacks with create_batch):

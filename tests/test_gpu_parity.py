@@ -298,3 +298,18 @@ def test_packed_projection(cuda):
         {"means": g.means, "quats": g.quats, "scales": g.log_scales}, g.viewmats, g.Ks, g.width,
         g.height, packed=False)
     assert r2.shape == (3, 800) and m2u.shape == (3, 800, 2) and d2u.shape == (3, 800)
+
+
+@pytest.mark.parametrize("n", [1, 2, 3, 1001, 2503])
+def test_backward_with_gaussian_counts_not_multiple_of_four(cuda, n):
+    """The flat [15 N] gradient puts the quaternion rows 12 N bytes in: not 16-byte aligned unless
+    N % 4 == 0.  Forward and backward must not care."""
+    sc = make_scene(n, 2, "tum", 0.25)
+    ref, (ps, vm), out, (gps, gvm) = _full(sc, cuda)
+    w = torch.rand(ref.rgbs.shape, generator=torch.Generator().manual_seed(3))
+    ((ref.rgbs * w).sum() + ref.alphas.sum()).backward()
+    ((out.rgbs * w.to(cuda)).sum() + out.alphas.sum()).backward()
+    for p, gp in zip(ps[:5], gps[:5]):
+        assert gp.grad is not None and bool(torch.isfinite(gp.grad).all())
+        if float(p.grad.norm()) > 0:
+            assert rel_err(gp.grad, p.grad) < GRAD_RTOL
