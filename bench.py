@@ -230,6 +230,61 @@ def mapping_leg(args, dev, rank, world):
                     "flat-gradient all-reduce, isotropic reg, fused Adam + opacity decay", "timed_loop": mode}
 
 
+def tracking_closure_leg(args, dev):
+    """The reference's own tracking iteration (gslam/frontend.py:604-662, the Adam phase of
+    igs_track_lbfgs): the map is frozen (no_grad clone, gslam/backend.py:515), only the frame's pose
+    (PoseZhou dR, dt) and exposure receive gradients; closure = splats([camera], [pose],
+    render_depth=True) -> exposure + active-NeRF tracking loss -> backward -> Adam step."""
+    import torch
+    from gslam_b200.graph import GraphedStep
+    from gslam_b200.losses import tracking_loss
+    from gslam_b200.map import GaussianSplattingData
+    from gslam_b200.optim import FusedAdam
+    from gslam_b200.primitives import Camera, PoseZhou
+    from gslam_b200.synthetic import make_scene, target_images
+
+    n = args.n_gauss
+    sc = make_scene(n, 1, "tum", 1.0).to(dev)
+    p = sc.params()
+    splats = GaussianSplattingData(p[0], p[1], p[2], p[3], p[4], p[5],
+                                   torch.zeros(n, dtype=torch.long, device=dev)).no_grad_clone()
+    cam = Camera(sc.Ks[0].clone(), sc.height, sc.width)
+    pose = PoseZhou(sc.viewmats[0].clone()).to(dev)
+    exposure = torch.zeros(2, device=dev, requires_grad=True)
+    gt = target_images(1, sc.height, sc.width).to(dev)
+    opt = FusedAdam([pose.dR, pose.dt, exposure], lr=3e-3, capturable=True)
+
+    def step():
+        for q in (pose.dR, pose.dt, exposure):
+            q.grad = None
+        out = splats([cam], [pose], render_depth=True)
+        loss = tracking_loss(out.render, gt, exposure, "active-nerf")
+        loss.backward()
+        opt.step()
+        return loss
+
+    gs = GraphedStep(step)
+    for _ in range(3):
+        gs.replay()
+    torch.cuda.synchronize()
+    steps = args.steps
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+    for e0, e1 in ev:
+        flush.zero_()
+        e0.record()
+        gs.replay()
+        e1.record()
+    torch.cuda.synchronize()
+    gs.check()
+    ms = sum(a.elapsed_time(b) for a, b in ev) / steps
+    return {"metric": "tracking closure it/s (frozen map, pose + exposure gradients, Adam step)",
+            "value": 1e3 / ms, "unit": "it/s", "ms_per_step": ms, "steps": steps, "n_gauss": n,
+            "step": "PoseZhou chain, render RGB+D+beta, exposure + active-NeRF loss, backward to dR/dt/exposure, "
+                    "fused Adam", "timed_loop": "CUDA-graph replay, L2 flushed between steps",
+            "launch_calls_per_step": gs.launches_per_replay}
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -433,6 +488,7 @@ def run_ours(args):
     mapping = None
     if not args.no_mapping:
         mapping = mapping_leg(args, dev, rank, world)
+    closure = tracking_closure_leg(args, dev) if rank == 0 else None
 
     if rank == 0:
         hbm, which, sm_max = peaks()
@@ -506,6 +562,7 @@ def run_ours(args):
             "roofline": roofline,
             "roofline_stages": stages,
             "mapping": mapping,
+            "tracking_closure": closure,
         }
         if world == 1 and not args.no_cpu_baseline:
             v, tsec, cores, sample = cpu_oracle_rate(n, band_rows=30, reps=1)

@@ -8,3 +8,4 @@ for s in d["roofline_stages"]:
 print("sum kernels us", round(tot*1000,1))
 
 if d.get("mapping"): print("mapping", round(d["mapping"]["value"],1), "views/s", round(d["mapping"]["ms_per_step"],4), "ms")
+if d.get("tracking_closure"): print("tracking_closure", round(d["tracking_closure"]["value"],1), "it/s", round(d["tracking_closure"]["ms_per_step"],4), "ms", d["tracking_closure"]["launch_calls_per_step"], "launches")
