@@ -16,8 +16,16 @@ __constant__ float G11[11] = {1.0283800845e-03f, 7.5987581352e-03f, 3.6000772128
                               3.6000772128e-02f, 7.5987581352e-03f, 1.0283800845e-03f};
 #define SSIM_C1 (0.01f * 0.01f)
 #define SSIM_C2 (0.03f * 0.03f)
-#define SB 16
-#define SH (SB + 10)
+// Tiling of the two SSIM kernels: a 256-thread CTA produces a 32 x 32 tile of one (image, channel)
+// plane.  The 11-tap window is separable; both passes are register-blocked so that a thread loads
+// 14 neighbours once for FOUR outputs (horizontal: 4 consecutive columns of one row; vertical: 4
+// consecutive rows of one column) -- 3.5 shared-memory loads per tap-sum instead of 11.  Row
+// strides are = 1 (mod 4) words, which makes the 4-row x 8-group access pattern of a warp hit 32
+// different banks.
+#define SB 32                   // tile edge
+#define SH (SB + 10)            // tile + halo
+#define SXS 45                  // row stride of the input tiles  (>= SH, = 1 mod 4)
+#define HCS 33                  // row stride of the row-filtered tiles (>= SB, = 1 mod 4)
 
 struct Strides4 {
     int64_t n, c, h, w;
@@ -37,65 +45,97 @@ __device__ __forceinline__ float block_sum_256(float v, float* red) {
     return s;   // valid in thread 0
 }
 
-// grid (ceil(W/16), ceil(H/16), N*C), block 256 (tx = tid & 15, ty = tid >> 4)
+// grid (ceil(W/32), ceil(H/32), N*C), block 256
 __global__ void __launch_bounds__(256)
 ssim_fwd_kernel(const float* __restrict__ img1, const float* __restrict__ img2, Strides4 s1, Strides4 s2,
                 int C, int H, int W, int valid, float* __restrict__ ssim_sum,
                 float* __restrict__ dm_dmu1, float* __restrict__ dm_ds1, float* __restrict__ dm_ds12) {
-    __shared__ float sx[SH][SH + 1], sy[SH][SH + 1];
-    __shared__ float hc[5][SH][SB];
+    __shared__ float sx[SH][SXS], sy[SH][SXS];
+    __shared__ float hc[5][SH][HCS];
     __shared__ float red[8];
     const int nc = blockIdx.z, n = nc / C, c = nc % C;
-    const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+    const int tid = threadIdx.x;
     const int h0 = blockIdx.y * SB, w0 = blockIdx.x * SB;
     const float* p1 = img1 + n * s1.n + c * s1.c;
     const float* p2 = img2 + n * s2.n + c * s2.c;
     for (int i = tid; i < SH * SH; i += 256) {
-        int r = i / SH, q = i % SH;
-        int gh = h0 + r - 5, gw = w0 + q - 5;
-        bool in = gh >= 0 && gh < H && gw >= 0 && gw < W;
+        const int r = i / SH, q = i - r * SH;
+        const int gh = h0 + r - 5, gw = w0 + q - 5;
+        const bool in = gh >= 0 && gh < H && gw >= 0 && gw < W;
         sx[r][q] = in ? p1[gh * s1.h + gw * s1.w] : 0.f;
         sy[r][q] = in ? p2[gh * s2.h + gw * s2.w] : 0.f;
     }
     __syncthreads();
-    for (int i = tid; i < SH * SB; i += 256) {
-        int r = i / SB, q = i % SB;
-        float m1 = 0.f, m2 = 0.f, xx = 0.f, yy = 0.f, xy = 0.f;
+    // horizontal pass: item = (row r, group of 4 columns)
+    for (int i = tid; i < SH * (SB / 4); i += 256) {
+        const int r = i / (SB / 4), q0 = (i - r * (SB / 4)) * 4;
+        float m1[4] = {0.f, 0.f, 0.f, 0.f}, m2[4] = {0.f, 0.f, 0.f, 0.f}, xx[4] = {0.f, 0.f, 0.f, 0.f};
+        float yy[4] = {0.f, 0.f, 0.f, 0.f}, xy[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-        for (int k = 0; k < 11; ++k) {
-            float x = sx[r][q + k], y = sy[r][q + k], w = G11[k];
-            m1 += w * x; m2 += w * y; xx += w * x * x; yy += w * y * y; xy += w * x * y;
+        for (int k = 0; k < 14; ++k) {
+            const float x = sx[r][q0 + k], y = sy[r][q0 + k];
+            const float x2 = x * x, y2 = y * y, xyv = x * y;
+#pragma unroll
+            for (int o = 0; o < 4; ++o) {
+                const int tap = k - o;          // compile-time after unrolling
+                if (tap >= 0 && tap < 11) {
+                    const float w = G11[tap];
+                    m1[o] = fmaf(w, x, m1[o]); m2[o] = fmaf(w, y, m2[o]);
+                    xx[o] = fmaf(w, x2, xx[o]); yy[o] = fmaf(w, y2, yy[o]); xy[o] = fmaf(w, xyv, xy[o]);
+                }
+            }
         }
-        hc[0][r][q] = m1; hc[1][r][q] = m2; hc[2][r][q] = xx; hc[3][r][q] = yy; hc[4][r][q] = xy;
+#pragma unroll
+        for (int o = 0; o < 4; ++o) {
+            hc[0][r][q0 + o] = m1[o]; hc[1][r][q0 + o] = m2[o]; hc[2][r][q0 + o] = xx[o];
+            hc[3][r][q0 + o] = yy[o]; hc[4][r][q0 + o] = xy[o];
+        }
     }
     __syncthreads();
-    float mu1 = 0.f, mu2 = 0.f, e11 = 0.f, e22 = 0.f, e12 = 0.f;
+    // vertical pass: thread = (column tx, group of 4 rows)
+    const int tx = tid & 31, ty0 = (tid >> 5) * 4;
+    float acc[5][4];
 #pragma unroll
-    for (int k = 0; k < 11; ++k) {
-        float w = G11[k];
-        mu1 += w * hc[0][ty + k][tx]; mu2 += w * hc[1][ty + k][tx]; e11 += w * hc[2][ty + k][tx];
-        e22 += w * hc[3][ty + k][tx]; e12 += w * hc[4][ty + k][tx];
-    }
-    const int h = h0 + ty, w = w0 + tx;
-    const bool inside = h < H && w < W;
-    const bool counted = inside && (!valid || (h >= 5 && h < H - 5 && w >= 5 && w < W - 5));
-    const float sg1 = e11 - mu1 * mu1, sg2 = e22 - mu2 * mu2, sg12 = e12 - mu1 * mu2;
-    const float A1 = 2.f * mu1 * mu2 + SSIM_C1, A2 = 2.f * sg12 + SSIM_C2;
-    const float B1 = mu1 * mu1 + mu2 * mu2 + SSIM_C1, B2 = sg1 + sg2 + SSIM_C2;
-    const float inv = 1.0f / (B1 * B2);
-    const float m = A1 * A2 * inv;
-    if (dm_dmu1 && inside) {
-        // m as a function of (mu1, E[x^2], E[xy]) with img2 fixed
-        float d_mu1 = 0.f, d_s1 = 0.f, d_s12 = 0.f;
-        if (counted) {
-            d_mu1 = (2.f * mu2 * (A2 - A1) * inv) - m * 2.f * mu1 * (B2 - B1) * inv;
-            d_s1 = -m / B2;
-            d_s12 = 2.f * A1 * inv;
+    for (int m = 0; m < 5; ++m) {
+#pragma unroll
+        for (int o = 0; o < 4; ++o) acc[m][o] = 0.f;
+#pragma unroll
+        for (int k = 0; k < 14; ++k) {
+            const float v = hc[m][ty0 + k][tx];
+#pragma unroll
+            for (int o = 0; o < 4; ++o) {
+                const int tap = k - o;
+                if (tap >= 0 && tap < 11) acc[m][o] = fmaf(G11[tap], v, acc[m][o]);
+            }
         }
-        size_t o = ((size_t)nc * H + h) * W + w;
-        dm_dmu1[o] = d_mu1; dm_ds1[o] = d_s1; dm_ds12[o] = d_s12;
     }
-    float tot = block_sum_256(counted ? m : 0.f, red);
+    float part = 0.f;
+    const int w = w0 + tx;
+#pragma unroll
+    for (int o = 0; o < 4; ++o) {
+        const int h = h0 + ty0 + o;
+        const float mu1 = acc[0][o], mu2 = acc[1][o], e11 = acc[2][o], e22 = acc[3][o], e12 = acc[4][o];
+        const bool inside = h < H && w < W;
+        const bool counted = inside && (!valid || (h >= 5 && h < H - 5 && w >= 5 && w < W - 5));
+        const float sg1 = e11 - mu1 * mu1, sg2 = e22 - mu2 * mu2, sg12 = e12 - mu1 * mu2;
+        const float A1 = 2.f * mu1 * mu2 + SSIM_C1, A2 = 2.f * sg12 + SSIM_C2;
+        const float B1 = mu1 * mu1 + mu2 * mu2 + SSIM_C1, B2 = sg1 + sg2 + SSIM_C2;
+        const float inv = 1.0f / (B1 * B2);
+        const float m = A1 * A2 * inv;
+        if (dm_dmu1 && inside) {
+            // m as a function of (mu1, E[x^2], E[xy]) with img2 fixed
+            float d_mu1 = 0.f, d_s1 = 0.f, d_s12 = 0.f;
+            if (counted) {
+                d_mu1 = (2.f * mu2 * (A2 - A1) * inv) - m * 2.f * mu1 * (B2 - B1) * inv;
+                d_s1 = -m / B2;
+                d_s12 = 2.f * A1 * inv;
+            }
+            const size_t o_ = ((size_t)nc * H + h) * W + w;
+            dm_dmu1[o_] = d_mu1; dm_ds1[o_] = d_s1; dm_ds12[o_] = d_s12;
+        }
+        part += counted ? m : 0.f;
+    }
+    const float tot = block_sum_256(part, red);
     if (tid == 0 && tot != 0.f) atomicAdd(ssim_sum, tot);
 }
 
@@ -105,46 +145,70 @@ ssim_bwd_kernel(const float* __restrict__ img1, const float* __restrict__ img2, 
                 int C, int H, int W, const float* __restrict__ dm_dmu1, const float* __restrict__ dm_ds1,
                 const float* __restrict__ dm_ds12, const float* __restrict__ grad, float coef,
                 float* __restrict__ v_img1, Strides4 so, int accumulate) {
-    __shared__ float sa[3][SH][SH + 1];
-    __shared__ float hc[3][SH][SB];
+    __shared__ float sa[3][SH][SXS];
+    __shared__ float hc[3][SH][HCS];
     const int nc = blockIdx.z, n = nc / C, c = nc % C;
-    const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+    const int tid = threadIdx.x;
     const int h0 = blockIdx.y * SB, w0 = blockIdx.x * SB;
     const size_t plane = (size_t)nc * H * W;
     for (int i = tid; i < SH * SH; i += 256) {
-        int r = i / SH, q = i % SH;
-        int gh = h0 + r - 5, gw = w0 + q - 5;
-        bool in = gh >= 0 && gh < H && gw >= 0 && gw < W;
-        size_t o = plane + (size_t)gh * W + gw;
+        const int r = i / SH, q = i - r * SH;
+        const int gh = h0 + r - 5, gw = w0 + q - 5;
+        const bool in = gh >= 0 && gh < H && gw >= 0 && gw < W;
+        const size_t o = plane + (size_t)gh * W + gw;
         sa[0][r][q] = in ? dm_dmu1[o] : 0.f;
         sa[1][r][q] = in ? dm_ds1[o] : 0.f;
         sa[2][r][q] = in ? dm_ds12[o] : 0.f;
     }
     __syncthreads();
-    for (int i = tid; i < SH * SB; i += 256) {
-        int r = i / SB, q = i % SB;
-        float a = 0.f, b = 0.f, d = 0.f;
+    for (int i = tid; i < SH * (SB / 4); i += 256) {
+        const int r = i / (SB / 4), q0 = (i - r * (SB / 4)) * 4;
 #pragma unroll
-        for (int k = 0; k < 11; ++k) {
-            float w = G11[k];
-            a += w * sa[0][r][q + k]; b += w * sa[1][r][q + k]; d += w * sa[2][r][q + k];
+        for (int m = 0; m < 3; ++m) {
+            float a[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+            for (int k = 0; k < 14; ++k) {
+                const float v = sa[m][r][q0 + k];
+#pragma unroll
+                for (int o = 0; o < 4; ++o) {
+                    const int tap = k - o;
+                    if (tap >= 0 && tap < 11) a[o] = fmaf(G11[tap], v, a[o]);
+                }
+            }
+#pragma unroll
+            for (int o = 0; o < 4; ++o) hc[m][r][q0 + o] = a[o];
         }
-        hc[0][r][q] = a; hc[1][r][q] = b; hc[2][r][q] = d;
     }
     __syncthreads();
-    float a = 0.f, b = 0.f, d = 0.f;
+    const int tx = tid & 31, ty0 = (tid >> 5) * 4;
+    float acc[3][4];
 #pragma unroll
-    for (int k = 0; k < 11; ++k) {
-        float w = G11[k];
-        a += w * hc[0][ty + k][tx]; b += w * hc[1][ty + k][tx]; d += w * hc[2][ty + k][tx];
+    for (int m = 0; m < 3; ++m) {
+#pragma unroll
+        for (int o = 0; o < 4; ++o) acc[m][o] = 0.f;
+#pragma unroll
+        for (int k = 0; k < 14; ++k) {
+            const float v = hc[m][ty0 + k][tx];
+#pragma unroll
+            for (int o = 0; o < 4; ++o) {
+                const int tap = k - o;
+                if (tap >= 0 && tap < 11) acc[m][o] = fmaf(G11[tap], v, acc[m][o]);
+            }
+        }
     }
-    const int h = h0 + ty, w = w0 + tx;
-    if (h >= H || w >= W) return;
-    const float x = img1[n * s1.n + c * s1.c + h * s1.h + w * s1.w];
-    const float y = img2[n * s2.n + c * s2.c + h * s2.h + w * s2.w];
-    const float g = (grad ? *grad : 1.0f) * coef * (a + 2.f * x * b + y * d);
-    float* dst = v_img1 + n * so.n + c * so.c + h * so.h + w * so.w;
-    *dst = accumulate ? *dst + g : g;
+    const int w = w0 + tx;
+    if (w >= W) return;
+    const float scale = (grad ? *grad : 1.0f) * coef;
+#pragma unroll
+    for (int o = 0; o < 4; ++o) {
+        const int h = h0 + ty0 + o;
+        if (h >= H) continue;
+        const float x = img1[n * s1.n + c * s1.c + h * s1.h + w * s1.w];
+        const float y = img2[n * s2.n + c * s2.c + h * s2.h + w * s2.w];
+        const float g = scale * (acc[0][o] + 2.f * x * acc[1][o] + y * acc[2][o]);
+        float* dst = v_img1 + n * so.n + c * so.c + h * so.h + w * so.w;
+        *dst = accumulate ? *dst + g : g;
+    }
 }
 
 static Strides4 mk(const int64_t* s) { return Strides4{s[0], s[1], s[2], s[3]}; }
