@@ -145,7 +145,16 @@ def ptr(t: Optional[torch.Tensor]):
     return t.data_ptr()
 
 
+_raw_stream = getattr(torch._C, "_cuda_getCurrentRawStream", None)
+_raw_device = getattr(torch._C, "_cuda_getDevice", None)
+
+
 def stream() -> int:
+    """cudaStream_t of torch's current stream on the current device.  The raw accessors are ~20x
+    cheaper than torch.cuda.current_stream() (17 us a call, 10 calls per step: a quarter of the host
+    time of an eager step); the public path is the fallback if a torch build lacks them."""
+    if _raw_stream is not None and _raw_device is not None:
+        return _raw_stream(_raw_device())
     return torch.cuda.current_stream().cuda_stream
 
 
