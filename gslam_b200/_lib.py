@@ -48,6 +48,8 @@ SIGNATURES = {
     "gsb_scale_by_scalar": (_i, [_p, _l, _p, _p]),
     "gsb_adam_multi": (_i, [_p, _i, _f, _f, _f, _i, _i, _p, _i, _f, _p, _p]),
     "gsb_composite_bwd": (_i, [_p] * 4 + [_i] * 6 + [_l] + [_p] * 6 + [_p]),
+    "gsb_vis_count": (_i, [_p, _i, _l, _p, _p]),
+    "gsb_isotropic_reg": (_i, [_p, _p, _l, _f, _p, _p, _p]),
     "gsb_rows_resize": (_i, [_p, _i, _l, _p, _l, _l, _p]),
     "gsb_pose_fwd": (_i, [_p, _p, _p, _i, _p, _p]),
     "gsb_pose_bwd": (_i, [_p, _p, _p, _i, _p, _p, _p]),

@@ -99,8 +99,8 @@ class _PhotometricSSIM(torch.autograd.Function):
             call("gsb_ssim_fwd", ptr(img1), ptr(img2), _strides(img1), _strides(img2), C, 3, H, W, 1,
                  ptr(ssim_sum), ptr(maps[0]), ptr(maps[1]), ptr(maps[2]), stream())
             ctx.count = C * 3 * (H - 10) * (W - 10)
-            ssim = ssim_sum[0] / ctx.count
-            total = total + ssim_weight * (1.0 - ssim)
+            # total + w * (1 - ssim_sum / count) in two launches
+            total = torch.sub(total, ssim_sum[0], alpha=ssim_weight / ctx.count) + ssim_weight
         ctx.save_for_backward(render, gt, maps, v_render, v_exp)
         ctx.ssim_weight = ssim_weight
         ctx.mark_non_differentiable(photo)

@@ -50,12 +50,19 @@ class FlatSplats:
             o += w * n
 
     def flat_grad(self) -> Tensor:
-        """The [15 N] gradient; zero-copy when the grads are still views of project_bwd's buffer."""
+        """The [15 N] gradient; zero-copy when the grads are still the six consecutive slices of
+        project_bwd's flat buffer (autograd hands them over detached, so this is decided from the
+        storage, not from `_base`)."""
         grads = [p.grad for p in self.params]
-        base = grads[0]._base if grads[0] is not None else None
-        if base is not None and base.numel() == 15 * self.n and all(
-                g is not None and g._base is base for g in grads):
-            return base
+        g0 = grads[0]
+        if g0 is not None and all(g is not None and g.is_contiguous() for g in grads):
+            st, o, ok = g0.untyped_storage(), g0.storage_offset(), True
+            expect = o
+            for g, w in zip(grads, PARAM_WIDTH):
+                ok = ok and g.untyped_storage().data_ptr() == st.data_ptr() and g.storage_offset() == expect
+                expect += w * self.n
+            if ok and st.nbytes() >= (o + 15 * self.n) * g0.element_size():
+                return torch.empty(0, dtype=g0.dtype, device=g0.device).set_(st, o, (15 * self.n,), (1,))
         flat = torch.cat([(g if g is not None else torch.zeros_like(p)).reshape(-1)
                           for g, p in zip(grads, self.params)])
         o = 0
@@ -66,9 +73,30 @@ class FlatSplats:
 
 
 @torch.no_grad()
+def visibility_count(radii: Tensor) -> Tensor:
+    """(radii > 0).sum(dim=0) as int32 [N] (gslam/backend.py:287, :357): one launch on CUDA."""
+    if radii.is_cuda:
+        from ._lib import call, ptr, stream
+        C, N = radii.shape
+        out = torch.empty(N, dtype=torch.int32, device=radii.device)
+        call("gsb_vis_count", ptr(radii.contiguous()), C, N, ptr(out), stream())
+        return out
+    return (radii > 0).sum(dim=0).to(torch.int32)
+
+
+@torch.no_grad()
 def add_isotropic_grad_(scales_grad: Tensor, log_scales: Tensor, visible: Tensor, weight: float):
     """d/d log_scales of  weight * sum_visible |exp(s) - exp(mean_axis s).detach()|
-    (gslam/backend.py:286-296), added in place; returns the loss value."""
+    (gslam/backend.py:286-296), added in place; returns the loss value.  `visible` is the int32
+    visibility count (or a bool mask).  CUDA tensors take one kernel (gsb_isotropic_reg); the torch
+    expression below serves the CPU host-logic tests of the mapping step (gloo, stub renderer)."""
+    if scales_grad.is_cuda and visible.dtype == torch.int32 and scales_grad.is_contiguous():
+        from ._lib import call, ptr, stream
+        loss = torch.zeros(1, dtype=torch.float32, device=scales_grad.device)
+        call("gsb_isotropic_reg", ptr(log_scales.detach().contiguous()), ptr(visible), log_scales.shape[0],
+             float(weight), ptr(scales_grad), ptr(loss), stream())
+        return loss[0]
+    visible = visible > 0 if visible.dtype != torch.bool else visible
     s = log_scales.detach()
     e = s.exp()
     m = s.mean(dim=1, keepdim=True).exp()
@@ -136,14 +164,14 @@ class MappingStep:
             # a sum (not a mean) over this rank's views: no share factor (gslam/backend.py:297-318)
             loss = loss + self.tv_w * edge_aware_tv(out.depthmaps, out.rgbs, out.alphas[..., 0] > 0.4)
         loss.backward()
-        vis_count = (out.radii > 0).sum(dim=0).to(torch.int32)
+        vis_count = visibility_count(out.radii)
         allreduce_sum_(vis_count, self.group)
         flat = self.splats.flat_grad()
         allreduce_sum_(flat, self.group)                      # the one gradient collective of the step
         # isotropic regulariser on the union visibility, identical on every rank, after the reduce
-        iso = add_isotropic_grad_(P[2].grad, P[2], vis_count > 0, self.iso_w)
+        iso = add_isotropic_grad_(P[2].grad, P[2], vis_count, self.iso_w)
         if step_optimizer:
             self.opt.step(decay_param=P[3], vis_count=vis_count, decay=self.decay)
-        stats = torch.stack([total.detach() * share, photo.detach() * share])
+        stats = torch.stack([total.detach(), photo.detach()]) * share
         allreduce_sum_(stats, self.group)
         return MappingStepResult(stats[0] + self.iso_w * iso, stats[1], out.radii, out.n_touched, vis_count)

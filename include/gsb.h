@@ -213,6 +213,15 @@ int gsb_adam_multi(const gsb_adam_tensor* tensors_host, int n_tensors, float bet
                    float eps, int step, int decay_tensor, const int32_t* vis_count, int vis_div,
                    float decay, int32_t* step_dev, void* stream);
 
+/* ---- per-Gaussian pieces of the mapping step between the big kernels ----------------------
+ * gsb_vis_count: vis_count[n] = #views with radii[c,n] > 0 (gslam/backend.py:287, :357).
+ * gsb_isotropic_reg: the isotropic regulariser of gslam/backend.py:288-296 on the Gaussians with
+ * vis_count > 0: adds weight * d/ds sum|exp(s) - exp(mean s).detach()| to v_log_scales[N,3] and the
+ * unweighted sum to *loss_sum (float, may be NULL, accumulated atomically). */
+int gsb_vis_count(const int32_t* radii, int C, int64_t N, int32_t* vis_count, void* stream);
+int gsb_isotropic_reg(const float* log_scales, const int32_t* vis_count, int64_t N, float weight,
+                      float* v_log_scales, float* loss_sum, void* stream);
+
 /* ---- densify / prune surgery ------------------------------------------------
  * Replaces the per-tensor `value[keep_mask]` / `torch.cat` loops of gslam/pruning.py:10-53 and
  * gslam/insertion.py:27-62 over the 6 parameters and their 12 Adam states: every listed tensor

@@ -57,3 +57,21 @@ def test_mapping_step_matches_oracle_step(cuda):
     p0 = FlatSplats(sc.params()).flat
     dr, do = ref.flat.detach() - p0, ours.flat.detach().cpu() - p0
     assert float((do - dr).norm() / dr.norm()) < 2e-2
+
+
+def test_visibility_count_and_isotropic_reg_kernels_match_torch(cuda):
+    """gsb_vis_count / gsb_isotropic_reg against the torch expressions of gslam/backend.py:287-296."""
+    from gslam_b200.mapping import add_isotropic_grad_, visibility_count
+    g = torch.Generator().manual_seed(0)
+    n = 10_007
+    radii = (torch.randint(-2, 6, (5, n), generator=g) * (torch.rand(5, n, generator=g) > 0.4)).to(torch.int32)
+    vc = visibility_count(radii.to(cuda))
+    assert vc.dtype == torch.int32 and torch.equal(vc.cpu(), (radii > 0).sum(0).to(torch.int32))
+    s = (-4.0 + 0.7 * torch.randn(n, 3, generator=g))
+    grad0 = torch.randn(n, 3, generator=g)
+    ref_grad = grad0.clone()
+    ref_loss = add_isotropic_grad_(ref_grad, s, (radii > 0).sum(0) > 0, 5e-4)         # CPU: torch expression
+    gpu_grad = grad0.clone().to(cuda)
+    gpu_loss = add_isotropic_grad_(gpu_grad, s.to(cuda), vc, 5e-4)                     # CUDA: one kernel
+    assert torch.allclose(gpu_grad.cpu(), ref_grad, rtol=1e-5, atol=1e-7)
+    assert abs(float(gpu_loss) - float(ref_loss)) < 1e-4 * abs(float(ref_loss))
