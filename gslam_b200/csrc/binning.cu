@@ -351,7 +351,7 @@ __device__ __forceinline__ void bucket_sort(const uint64_t* in, uint64_t* out, i
 // so a 2048-key configuration keeps nine CTAs per SM resident.  Longer segments take the
 // generic path through global scratch.
 template <int KPT>
-__global__ void __launch_bounds__(SEG_THREADS)
+__global__ void __launch_bounds__(SEG_THREADS, KPT == 8 ? 6 : (KPT == 16 ? 4 : 2))   // what shared memory allows
 segment_sort_kernel(uint64_t* __restrict__ dk, uint64_t* __restrict__ tmp,
                     const int32_t* __restrict__ offsets, int n_tiles, int tile_n_bits, int64_t capacity,
                     int64_t* __restrict__ isect_ids, int32_t* __restrict__ flatten_ids) {
@@ -390,8 +390,7 @@ segment_sort_kernel(uint64_t* __restrict__ dk, uint64_t* __restrict__ tmp,
                 mn = min(mn, d); mx = max(mx, d);
             }
         }
-        int lgB = 0;
-        while ((1 << lgB) < L) ++lgB;           // L <= ELEMS, a power of two
+        const int lgB = 32 - __clz(L - 1);      // L >= 2; L <= ELEMS, a power of two
         const int B = 1 << lgB;
         mn = __reduce_min_sync(0xffffffffu, mn);
         mx = __reduce_max_sync(0xffffffffu, mx);
@@ -424,8 +423,8 @@ segment_sort_kernel(uint64_t* __restrict__ dk, uint64_t* __restrict__ tmp,
             }
             if (lane == 31) warp_sum_s[warp] = x;
             __syncthreads();
-            int base = 0;
-            for (int w = 0; w < warp; ++w) base += warp_sum_s[w];
+            // sum of the warps before this one (SEG_THREADS / 32 <= 32 of them)
+            const int base = __reduce_add_sync(0xffffffffu, lane < warp ? warp_sum_s[lane] : 0);
             int run = base + x - local;
             if (b0 < B)
                 for (int k = 0; k < per; ++k) {
@@ -435,35 +434,48 @@ segment_sort_kernel(uint64_t* __restrict__ dk, uint64_t* __restrict__ tmp,
                 }
         }
         __syncthreads();
+        int slot[KPT];      // where the scatter put each key
 #pragma unroll
-        for (int i = 0; i < KPT; ++i)
-            if (tid + i * SEG_THREADS < L) out[atomicAdd(&cnt[bucket_of(key[i])], 1)] = key[i];
-        __syncthreads();
-        // cnt[b] is now the end of bucket b; finish the buckets
-        for (int bkt = tid; bkt < B; bkt += SEG_THREADS) {
-            const int s0 = bkt ? cnt[bkt - 1] : 0, m = cnt[bkt] - s0;
-            if (m < 2) continue;
-            bool small = m <= SEG_SMALL;
-            if (!small) {
-                int slot = atomicAdd(&n_big, 1);
-                if (slot < SEG_MAX_BIG) big[slot] = bkt;
-                else small = true;          // list full: slow but correct
+        for (int i = 0; i < KPT; ++i) {
+            slot[i] = -1;
+            if (tid + i * SEG_THREADS < L) {
+                slot[i] = atomicAdd(&cnt[bucket_of(key[i])], 1);
+                out[slot[i]] = key[i];
             }
-            if (small) {
-                for (int i = 1; i < m; ++i) {
-                    uint64_t k = out[s0 + i];
-                    int j = i - 1;
-                    while (j >= 0 && out[s0 + j] > k) { out[s0 + j + 1] = out[s0 + j]; --j; }
-                    out[s0 + j + 1] = k;
+        }
+        __syncthreads();
+        // cnt[b] is now the end of bucket b.  Every key ranks itself inside its bucket (keys are
+        // unique: the low word is the flatten id) -- m reads per key, all keys in parallel, instead of
+        // one thread insertion-sorting a whole bucket while its warp waits.  Buckets above SEG_SMALL
+        // keys (heavily clustered depths) are left as scattered and bitonic-sorted by the whole CTA.
+#pragma unroll
+        for (int i = 0; i < KPT; ++i) {
+            if (slot[i] >= 0) {
+                const int b = bucket_of(key[i]);
+                const int s0 = b ? cnt[b - 1] : 0, m = cnt[b] - s0;
+                if (m > SEG_SMALL) {
+                    if (slot[i] == s0) {            // one key per bucket reports it
+                        const int q = atomicAdd(&n_big, 1);
+                        if (q < SEG_MAX_BIG) big[q] = b;
+                    }
+                } else if (m > 1) {
+                    int r = 0;
+                    for (int j = 0; j < m; ++j) r += out[s0 + j] < key[i];
+                    slot[i] = s0 + r;       // from here on: the key's final position
                 }
             }
         }
+        __syncthreads();
+#pragma unroll
+        for (int i = 0; i < KPT; ++i)
+            if (slot[i] >= 0) out[slot[i]] = key[i];
         __syncthreads();
         const int nb = min(n_big, SEG_MAX_BIG);
         for (int k = 0; k < nb; ++k) {
             const int bkt = big[k], s0 = bkt ? cnt[bkt - 1] : 0;
             bitonic_sort(out + s0, cnt[bkt] - s0);
         }
+        if (n_big > SEG_MAX_BIG) bitonic_sort(out, L);      // list full: slow but correct
         sorted = out;
     }
     __syncthreads();
