@@ -49,25 +49,32 @@ class FlatSplats:
             self.params.append(v.requires_grad_(True))
             o += w * n
 
-    def flat_grad(self) -> Tensor:
-        """The [15 N] gradient; zero-copy when the grads are still the six consecutive slices of
-        project_bwd's flat buffer (autograd hands them over detached, so this is decided from the
-        storage, not from `_base`)."""
+    def flat_grad(self, tail: int = 0) -> Tensor:
+        """The gradient as ONE buffer [15 N + tail]: the six gradients in parameter order, then `tail`
+        scratch floats (uninitialised) that ride along in the same all-reduce.  Zero-copy when the
+        grads are still the six consecutive slices of project_bwd's flat buffer and that buffer was
+        allocated with room for the tail (ops.grad_tail_floats); autograd hands the grads over
+        detached, so this is decided from the storage, not from `_base`."""
         grads = [p.grad for p in self.params]
         g0 = grads[0]
+        total = 15 * self.n + tail
         if g0 is not None and all(g is not None and g.is_contiguous() for g in grads):
             st, o, ok = g0.untyped_storage(), g0.storage_offset(), True
             expect = o
             for g, w in zip(grads, PARAM_WIDTH):
                 ok = ok and g.untyped_storage().data_ptr() == st.data_ptr() and g.storage_offset() == expect
                 expect += w * self.n
-            if ok and st.nbytes() >= (o + 15 * self.n) * g0.element_size():
-                return torch.empty(0, dtype=g0.dtype, device=g0.device).set_(st, o, (15 * self.n,), (1,))
-        flat = torch.cat([(g if g is not None else torch.zeros_like(p)).reshape(-1)
-                          for g, p in zip(grads, self.params)])
+            if ok and st.nbytes() >= (o + total) * g0.element_size():
+                return torch.empty(0, dtype=g0.dtype, device=g0.device).set_(st, o, (total,), (1,))
+        flat = torch.empty(total, dtype=self.flat.dtype, device=self.flat.device)
         o = 0
-        for p, w in zip(self.params, PARAM_WIDTH):
-            p.grad = flat[o:o + w * self.n].view(p.shape)
+        for p, g, w in zip(self.params, grads, PARAM_WIDTH):
+            dst = flat[o:o + w * self.n].view(p.shape)
+            if g is None:
+                dst.zero_()
+            else:
+                dst.copy_(g)
+            p.grad = dst
             o += w * self.n
         return flat
 
@@ -163,15 +170,23 @@ class MappingStep:
         if self.tv_w:
             # a sum (not a mean) over this rank's views: no share factor (gslam/backend.py:297-318)
             loss = loss + self.tv_w * edge_aware_tv(out.depthmaps, out.rgbs, out.alphas[..., 0] > 0.4)
-        loss.backward()
-        vis_count = visibility_count(out.radii)
-        allreduce_sum_(vis_count, self.group)
-        flat = self.splats.flat_grad()
-        allreduce_sum_(flat, self.group)                      # the one gradient collective of the step
+        from . import ops
+        n = self.splats.n
+        ops.grad_tail_floats = n + 2          # room behind the flat gradient for counts and loss scalars
+        try:
+            loss.backward()
+        finally:
+            ops.grad_tail_floats = 0
+        # ONE collective per step: [15 N gradient | N visibility counts | total, photometric]
+        buf = self.splats.flat_grad(tail=n + 2)
+        t_vis, t_stats = buf[15 * n:16 * n], buf[16 * n:]
+        t_vis.copy_(visibility_count(out.radii))            # exact in float32 (counts <= #views)
+        t_stats.copy_(torch.stack([total.detach(), photo.detach()]) * share)
+        allreduce_sum_(buf, self.group)
+        vis_count = t_vis.to(torch.int32)
+        stats = t_stats
         # isotropic regulariser on the union visibility, identical on every rank, after the reduce
         iso = add_isotropic_grad_(P[2].grad, P[2], vis_count, self.iso_w)
         if step_optimizer:
             self.opt.step(decay_param=P[3], vis_count=vis_count, decay=self.decay)
-        stats = torch.stack([total.detach(), photo.detach()]) * share
-        allreduce_sum_(stats, self.group)
         return MappingStepResult(stats[0] + self.iso_w * iso, stats[1], out.radii, out.n_touched, vis_count)

@@ -27,6 +27,10 @@ CSTRIDE = 32   # GSB_CSTRIDE: one per-tile counter per 128-byte line
 # bench.py sets this to a zeroed int64[1] CUDA tensor to collect P (pairs evaluated); None otherwise
 pair_counter: Optional[Tensor] = None
 
+# extra floats allocated behind the flat [15 N] gradient buffer of _Project.backward: the mapping step
+# parks its visibility counts and loss scalars there so that ONE all-reduce carries everything
+grad_tail_floats: int = 0
+
 
 def _c(t: Optional[Tensor]) -> Optional[Tensor]:
     if t is None:
@@ -104,7 +108,7 @@ class _Project(torch.autograd.Function):
         if need_gauss:
             # one flat buffer, means|quats|scales|opacities|colors|log_unc, so that a
             # view-sharded mapping step can all-reduce the six gradients in ONE call
-            flat = torch.empty(N * 15, dtype=torch.float32, device=dev)
+            flat = torch.empty(N * 15 + grad_tail_floats, dtype=torch.float32, device=dev)
             v_means = flat[0:3 * N].view(N, 3)
             v_quats = flat[3 * N:7 * N].view(N, 4)
             v_scales = flat[7 * N:10 * N].view(N, 3)
