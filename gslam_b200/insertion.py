@@ -1,0 +1,143 @@
+"""Keyframe insertion from a depth map, on the flat splat layout.
+
+Follows the algorithm of reference `InsertFromDepthMap.step` (gslam/insertion.py:117-273):
+
+1. pixels with rendered alpha above a threshold and positive depth count as "covered"; up to N new
+   splats go to uncovered pixels first, and (optionally) up to N/2 minus that many to covered ones;
+2. the depth of a new splat is the rendered depth plus noise where covered, the median covered
+   depth plus (larger) noise elsewhere, clamped to 0.1;
+3. the chosen pixels are back-projected with the frame's intrinsics and moved to world space with
+   the inverse of the frame's view matrix; colour = logit of the image, scale = the map's median
+   scale, quaternion random, opacity / uncertainty at their initial values;
+4. a candidate that lies IN FRONT of the estimated depth of any earlier keyframe at the pixel it
+   projects to is dropped (packed projection, `get_new_splat_depth`, gslam/rasterization.py:363-448);
+5. the survivors are appended to the parameters and to the Adam state in one launch
+   (`surgery.add_new_splats`, replacing `_add_new_splats`, gslam/insertion.py:27-62).
+
+Every tensor operation runs on the device; the two host reads are the covered-pixel count (as in
+the reference, :137) and the number of survivors that sizes the new buffers.  Random choices take an
+optional `torch.Generator` so that tests are repeatable.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import Dict, List, Optional, Sequence
+
+import torch
+from torch import Tensor
+
+from .mapping import FlatSplats
+from .rasterization import RasterizationOutput, get_new_splat_depth
+from .surgery import add_new_splats
+
+
+@dataclass
+class KeyframeView:
+    """What step 4 needs from an earlier keyframe (Frame.camera.intrinsics, Frame.pose(), Frame.est_depths)."""
+    intrinsics: Tensor      # [3,3]
+    viewmat: Tensor         # [4,4] world -> camera
+    est_depths: Tensor      # [H,W]
+
+
+def backproject(intrinsics: Tensor, depth_map: Tensor) -> Tensor:
+    """Camera-space points [H*W, 3] of a depth map (Camera.backproject, gslam/primitives.py:369-395)."""
+    H, W = depth_map.shape
+    fx, fy, cx, cy = intrinsics[0, 0], intrinsics[1, 1], intrinsics[0, 2], intrinsics[1, 2]
+    v, u = torch.meshgrid(torch.arange(H, device=depth_map.device, dtype=depth_map.dtype),
+                          torch.arange(W, device=depth_map.device, dtype=depth_map.dtype), indexing="ij")
+    x = (u - cx) * (depth_map / fx)
+    y = (v - cy) * (depth_map / fy)
+    return torch.stack([x, y, depth_map], dim=-1).reshape(-1, 3)
+
+
+class InsertFromDepthMap:
+    def __init__(self, depth_variance: float, no_depth_variance: float, min_alpha_for_depth: float,
+                 initial_opacity: float, insert_in_regions_with_depth: bool = True):
+        self.depth_variance = depth_variance
+        self.no_depth_variance = no_depth_variance
+        self.min_alpha_for_depth = min_alpha_for_depth
+        self.initial_opacity = initial_opacity
+        self.insert_in_regions_with_depth = insert_in_regions_with_depth
+
+    @torch.no_grad()
+    def propose(self, rasterization_output: RasterizationOutput, intrinsics: Tensor, viewmat: Tensor,
+                img: Tensor, median_scale: Optional[Tensor], N: int, gt_depthmap: Optional[Tensor] = None,
+                generator: Optional[torch.Generator] = None) -> Optional[Dict[str, Tensor]]:
+        """Steps 1-3: the candidate splats (parameter dict in the map's activation space) or None."""
+        depths = (rasterization_output.depthmaps[0] if gt_depthmap is None else gt_depthmap).clone()
+        alphas = rasterization_output.alphas[0, ..., 0]
+        dev = depths.device
+        covered = (alphas > self.min_alpha_for_depth) & (depths > 0)
+        n_covered = int(covered.sum().item())
+        n_open = depths.numel() - n_covered
+        n_in_open = min(N, n_open)
+        n_in_covered = max(0, min(N // 2 - n_in_open, n_covered))
+        if n_in_open <= 0 and not (self.insert_in_regions_with_depth and n_in_covered > 0):
+            return None
+        median_depth = depths[covered].median() if n_covered else depths.median()
+        noise = torch.randn(depths.shape, device=dev, dtype=depths.dtype, generator=generator)
+        depths = torch.where(covered, depths + noise * self.depth_variance,
+                             median_depth + noise * self.no_depth_variance).clamp_min_(0.1)
+        flat_cov = covered.reshape(-1)
+        picks: List[Tensor] = []
+        for mask, count in ((~flat_cov, n_in_open),
+                            (flat_cov, n_in_covered if self.insert_in_regions_with_depth else 0)):
+            if count > 0:
+                pool = torch.nonzero(mask).reshape(-1)
+                picks.append(pool[torch.randint(pool.shape[0], (count,), device=dev, generator=generator)])
+        if not picks:
+            return None
+        pick = torch.cat(picks)
+        n = pick.shape[0]
+        cam_pts = backproject(intrinsics, depths)[pick]
+        c2w = torch.linalg.inv(viewmat)
+        means = cam_pts @ c2w[:3, :3].t() + c2w[:3, 3]
+        colors = img.reshape(-1, 3)[pick].clamp(1e-4, 1 - 1e-4)      # logit of exact 0 / 1 is infinite
+        if median_scale is None:
+            # no map yet: a scale from the spacing of the new points (the reference uses a 3-NN distance)
+            spread = (means - means.mean(0)).norm(dim=1).mean() / max(n, 1) ** (1.0 / 3.0)
+            median_scale = spread.clamp_min(1e-4).expand(3)
+        return {
+            "means": means,
+            "scales": torch.log(median_scale).expand(n, 3).contiguous(),
+            "colors": torch.logit(colors),
+            "opacities": torch.logit(torch.full((n,), self.initial_opacity, device=dev)),
+            "quats": torch.rand(n, 4, device=dev, generator=generator),
+            "log_uncertainties": torch.ones(n, device=dev),
+        }
+
+    @torch.no_grad()
+    def occlusion_filter(self, new_params: Dict[str, Tensor], keyframes: Sequence[KeyframeView], width: int,
+                         height: int) -> Tensor:
+        """Step 4: keep mask [n]; False where a candidate is in front of an earlier keyframe's depth."""
+        n = new_params["means"].shape[0]
+        keep = torch.ones(n, dtype=torch.bool, device=new_params["means"].device)
+        if len(keyframes) <= 1 or n == 0:
+            return keep
+        Ks = torch.stack([k.intrinsics for k in keyframes])
+        viewmats = torch.stack([k.viewmat for k in keyframes])
+        est = torch.stack([k.est_depths for k in keyframes])
+        camera_ids, gaussian_ids, _, means2d, depths = get_new_splat_depth(new_params, viewmats, Ks, width, height)
+        px = means2d.to(torch.long)
+        col = px[:, 0].clamp(0, width - 1)
+        row = px[:, 1].clamp(0, height - 1)
+        in_front = depths < est[camera_ids, row, col]
+        keep[gaussian_ids[in_front]] = False
+        return keep
+
+    @torch.no_grad()
+    def step(self, splats: FlatSplats, optimizer, rasterization_output: RasterizationOutput,
+             intrinsics: Tensor, viewmat: Tensor, img: Tensor, N: int,
+             keyframes: Sequence[KeyframeView] = (), gt_depthmap: Optional[Tensor] = None,
+             generator: Optional[torch.Generator] = None) -> int:
+        """Insert up to N splats seen from (intrinsics, viewmat); returns how many were added."""
+        median_scale = torch.exp(splats.params[2].detach()).median(dim=0)[0] if splats.n else None
+        new_params = self.propose(rasterization_output, intrinsics, viewmat, img, median_scale, N,
+                                  gt_depthmap, generator)
+        if new_params is None:
+            return 0
+        H, W = rasterization_output.alphas.shape[1:3]
+        keep = self.occlusion_filter(new_params, keyframes, W, H)
+        if not bool(keep.all()):
+            new_params = {k: v[keep] for k, v in new_params.items()}
+        return add_new_splats(splats, optimizer, new_params)
