@@ -96,3 +96,27 @@ def test_prune_and_append_in_one_launch_and_edge_masks(cuda):
     ref = [p.detach()[keep2] for p in s2.params]
     prune_using_mask(s2, None, keep2)
     assert all(torch.equal(a.detach(), b) for a, b in zip(s2.params, ref))
+
+
+def test_prune_round_criteria(cuda):
+    """gslam/pruning.py:61-139 + gslam/backend.py:364-391 on the flat layout."""
+    from gslam_b200.pruning import (ill_conditioned_mask, large_footprint_mask, low_opacity_mask,
+                                    prune_round, young_and_unseen_mask)
+    sc, splats, opt = _setup(cuda, n=4000)
+    n = splats.n
+    g = torch.Generator().manual_seed(2)
+    radii = torch.randint(0, 60, (3, n), generator=g).to(torch.int32).to(cuda)
+    n_touched = (torch.randint(0, 5, (3, n), generator=g) * (torch.rand(3, n, generator=g) > 0.3)).to(cuda)
+    lo = low_opacity_mask(splats.params[3].detach(), 0.3)
+    big = large_footprint_mask(radii, 55)
+    ill = ill_conditioned_mask(radii, n_touched, 1)
+    assert torch.equal(big, radii.max(0).values > 55)
+    assert torch.equal(ill, ((radii > 0) & (n_touched == 0)).sum(0) > 1)
+    ages = torch.randint(0, 10, (n,), generator=g).to(cuda)
+    vis = torch.randint(0, 4, (n,), generator=g).to(cuda)
+    assert torch.equal(young_and_unseen_mask(ages, vis, 9, 2), (ages > 6) & (vis < 2))
+    expect_remove = lo | big | ill
+    kept_means = splats.params[0].detach()[~expect_remove].clone()
+    removed = prune_round(splats, opt, radii, n_touched, 0.3, 55, max_unproductive_views=1)
+    assert removed == int(expect_remove.sum()) and 0 < removed < n
+    assert torch.equal(splats.params[0].detach(), kept_means)
