@@ -48,6 +48,9 @@ def parse():
     ap.add_argument("--map-gauss", type=int, default=500_000)
     ap.add_argument("--no-mapping", action="store_true")
     ap.add_argument("--map-eager", action="store_true")
+    ap.add_argument("--track-frames", type=int, default=12)
+    ap.add_argument("--slam-frames", type=int, default=60)
+    ap.add_argument("--no-sequence", action="store_true")
     return ap.parse_args()
 
 
@@ -285,6 +288,62 @@ def tracking_closure_leg(args, dev):
             "launch_calls_per_step": gs.launches_per_replay}
 
 
+def tracking_frames_leg(args, dev):
+    """BASELINE cfg2 as the reference really schedules it (gslam/frontend.py:604-662): per frame 10
+    Adam steps + torch L-BFGS (strong Wolfe, <= 25 evaluations) on a frozen 200k-Gaussian map,
+    gslam_b200.tracking.Tracker; wall clock per frame (the L-BFGS phase is host-driven), every
+    frame a new image and the constant-motion start."""
+    import time
+    import torch
+    from gslam_b200.map import GaussianSplattingData
+    from gslam_b200.primitives import Camera
+    from gslam_b200.synthetic import make_scene, smooth_trajectory
+    from gslam_b200.tracking import Tracker, TrackingConfig, constant_motion
+    from gslam_b200 import _lib
+
+    n, F = args.n_gauss, args.track_frames
+    sc = make_scene(n, 1, "tum", 1.0).to(dev)
+    splats = GaussianSplattingData(*sc.params(), torch.zeros(n, dtype=torch.long, device=dev)).no_grad_clone()
+    cam = Camera(sc.Ks[0].clone(), sc.height, sc.width)
+    poses = smooth_trajectory(F + 2).to(dev)
+    with torch.no_grad():
+        imgs = [splats.render([cam], [poses[i]]).rgbs[0].clamp(0, 1).clone() for i in range(F + 2)]
+    tr = Tracker(cam, TrackingConfig(), dev)
+    tr.set_map(splats)
+    est = [poses[0].clone()]
+    est.append(tr.track_lbfgs(imgs[1], est[0]).viewmat)      # untimed: captures both graphs
+    torch.cuda.synchronize()
+    evals = syncs = 0
+    launches0 = _lib.launch_count
+    t0 = time.perf_counter()
+    for i in range(2, F + 2):
+        r = tr.track_lbfgs(imgs[i], constant_motion(est[-2], est[-1]))
+        est.append(r.viewmat)
+        evals += r.n_evals
+        syncs += r.n_syncs
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    err = float((torch.stack(est[2:])[:, :3, 3] - poses[2:, :3, 3]).norm(dim=1).mean())
+    return {"metric": "tracking frames/s (10 Adam + L-BFGS strong-Wolfe per frame, frozen map)",
+            "value": F / dt, "unit": "frames/s", "frames": F, "n_gauss": n, "evals_per_frame": evals / F,
+            "host_syncs_per_frame": syncs / F, "ms_per_eval": 1e3 * dt / max(evals, 1),
+            "mean_translation_error_m": err, "timed_loop": "wall clock; graph replay per evaluation"}
+
+
+def slam_sequence_leg(args, dev):
+    """BASELINE cfg5: synthetic sequence through tracking + mapping + insertion / pruning
+    (gslam_b200.slam, the inline equivalent of main.py), frames/s by wall clock."""
+    from gslam_b200.slam import run_sequence
+    F = args.slam_frames
+    slam, fps, _ = run_sequence(F, n_gauss=20_000, scale=1.0, device=dev)
+    st = slam.stats
+    return {"metric": "sequence frames/s (tracking + mapping + insertion/pruning, 640x480)", "value": fps,
+            "unit": "frames/s", "frames": F, "keyframes": st.keyframes, "n_splats": st.n_splats,
+            "mapping_iters": st.mapping_iters, "tracking_evals": st.tracking_evals,
+            "inserted": st.inserted, "pruned": st.pruned, "s_tracking": st.t_tracking,
+            "s_mapping": st.t_mapping, "includes": "frame 0 initialisation (400 mapping iterations)"}
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -489,6 +548,17 @@ def run_ours(args):
     if not args.no_mapping:
         mapping = mapping_leg(args, dev, rank, world)
     closure = tracking_closure_leg(args, dev) if rank == 0 else None
+    track_frames = slam_seq = None
+    if rank == 0 and not args.no_sequence:
+        # secondary legs: a failure here is reported in place and must not take the headline line down
+        try:
+            track_frames = tracking_frames_leg(args, dev)
+        except Exception as e:   # noqa: BLE001
+            track_frames = {"error": f"{type(e).__name__}: {e}"}
+        try:
+            slam_seq = slam_sequence_leg(args, dev)
+        except Exception as e:   # noqa: BLE001
+            slam_seq = {"error": f"{type(e).__name__}: {e}"}
 
     if rank == 0:
         hbm, which, sm_max = peaks()
@@ -563,6 +633,8 @@ def run_ours(args):
             "roofline_stages": stages,
             "mapping": mapping,
             "tracking_closure": closure,
+            "tracking_frames": track_frames,
+            "sequence": slam_seq,
         }
         if world == 1 and not args.no_cpu_baseline:
             v, tsec, cores, sample = cpu_oracle_rate(n, band_rows=30, reps=1)

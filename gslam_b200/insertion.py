@@ -50,6 +50,20 @@ def backproject(intrinsics: Tensor, depth_map: Tensor) -> Tensor:
     return torch.stack([x, y, depth_map], dim=-1).reshape(-1, 3)
 
 
+def knn_mean_distance(points: Tensor, k: int = 3, chunk: int = 4096) -> Tensor:
+    """Mean distance of every point [n,3] to its k nearest neighbours (the `knn(means, 4)[:, 1:]` of
+    gslam/insertion.py:226-230); dense distances in row chunks -- n is at most a few thousand here."""
+    n = points.shape[0]
+    if n <= 1:
+        return torch.ones(n, device=points.device, dtype=points.dtype)
+    kk = min(k, n - 1)
+    out = []
+    for i in range(0, n, chunk):
+        d = torch.cdist(points[i:i + chunk], points)
+        out.append(d.topk(kk + 1, dim=1, largest=False).values[:, 1:].mean(dim=1))
+    return torch.cat(out)
+
+
 class InsertFromDepthMap:
     def __init__(self, depth_variance: float, no_depth_variance: float, min_alpha_for_depth: float,
                  initial_opacity: float, insert_in_regions_with_depth: bool = True):
@@ -94,12 +108,13 @@ class InsertFromDepthMap:
         means = cam_pts @ c2w[:3, :3].t() + c2w[:3, 3]
         colors = img.reshape(-1, 3)[pick].clamp(1e-4, 1 - 1e-4)      # logit of exact 0 / 1 is infinite
         if median_scale is None:
-            # no map yet: a scale from the spacing of the new points (the reference uses a 3-NN distance)
-            spread = (means - means.mean(0)).norm(dim=1).mean() / max(n, 1) ** (1.0 / 3.0)
-            median_scale = spread.clamp_min(1e-4).expand(3)
+            # no map yet: each splat's scale is its mean distance to its 3 nearest neighbours (:226-231)
+            scales = knn_mean_distance(means, 3).clamp_min(1e-6).unsqueeze(-1).repeat(1, 3)
+        else:
+            scales = median_scale.expand(n, 3)
         return {
             "means": means,
-            "scales": torch.log(median_scale).expand(n, 3).contiguous(),
+            "scales": torch.log(scales).contiguous(),
             "colors": torch.logit(colors),
             "opacities": torch.logit(torch.full((n,), self.initial_opacity, device=dev)),
             "quats": torch.rand(n, 4, device=dev, generator=generator),

@@ -135,6 +135,7 @@ class MappingStepResult:
     radii: Tensor
     n_touched: Tensor
     vis_count: Tensor
+    outputs: Optional[object] = None     # this rank's RasterizationOutput (est. depths, means2d.grad, ...)
 
 
 class MappingStep:
@@ -189,4 +190,4 @@ class MappingStep:
         iso = add_isotropic_grad_(P[2].grad, P[2], vis_count, self.iso_w)
         if step_optimizer:
             self.opt.step(decay_param=P[3], vis_count=vis_count, decay=self.decay)
-        return MappingStepResult(stats[0] + self.iso_w * iso, stats[1], out.radii, out.n_touched, vis_count)
+        return MappingStepResult(stats[0] + self.iso_w * iso, stats[1], out.radii, out.n_touched, vis_count, out)

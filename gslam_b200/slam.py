@@ -1,0 +1,316 @@
+"""Headless tracking + mapping loop over a frame sequence (BASELINE cfg5; the callers either side
+of the render path).
+
+The reference runs this as three processes joined by queues (main.py:61-94): the sensor stream,
+`Frontend.run` (gslam/frontend.py) and `Backend.run` (gslam/backend.py:797-898).  Queues, process
+start-up, rerun / viser logging and dataset readers are control plane and stay out of scope; what
+is kept is the ORDER OF WORK on the render path, executed inline on one CUDA stream:
+
+    frame 0      Backend.initialize (:604-631): 5000 splats from a mock depth map, then
+                 optimize_map(num_iters_initialization, prune=False), sync
+    frame i > 0  Frontend.track (frontend.py:170-247): constant-motion start, igs_track_lbfgs
+                 Backend, ADD_FRAME (:856-873): to_insert_keyframe (:741-795) -> add_keyframe
+                 (:633-679) -> optimize_map(1, prune=True, regularize=False); sync every 5th frame
+                 Backend, idle (:846-852): optimize_map() [+ run_pruning] until StopOnPlateau pauses it
+
+Every step is the corresponding module of this package: `tracking.Tracker` (CUDA-graph closure),
+`mapping.MappingStep` (flat [15 N] layout, fused losses, one-launch Adam), `insertion.
+InsertFromDepthMap`, `pruning.prune_round`, `surgery` (one-launch append / compaction).  The map
+hand-off of `Backend.sync` -> `Frontend.sync` (deepcopy + pickle through an mp.Queue in the
+reference, backend.py:508-519) is one device-to-device copy of the flat parameter buffer
+(`Tracker.set_map`).
+
+Not reproduced: `InsertUsingImagePlaneGradients` (every 200th step, :328-336), the pose-graph /
+loop-closure bookkeeping (`enable_pgo`, off by default) and `optimize_poses_lbfgs` (:436-506).
+"""
+from __future__ import annotations
+
+import math
+import time
+from dataclasses import dataclass, field
+from typing import Dict, List, Optional
+
+import torch
+from torch import Tensor
+
+from .insertion import InsertFromDepthMap, KeyframeView
+from .map import GaussianSplattingData
+from .mapping import DEFAULT_LRS, PARAM_NAMES, FlatSplats, MappingStep
+from .optim import FusedAdam
+from .primitives import Camera, PoseZhou, pose_batch
+from .pruning import prune_round
+from .rasterization import RasterizationOutput, rasterization
+from .tracking import StopOnPlateau, Tracker, TrackingConfig, constant_motion
+
+
+@dataclass
+class MapConfig:
+    """The fields of the reference MapConfig (gslam/backend.py:43-113) this loop reads, same defaults."""
+    isotropic_regularization_weight: float = 0.0005
+    depth_regularization_weight: float = 0.000001
+    pose_optim_lr: float = 0.003
+    opacity_decay: float = 0.995
+    initial_opacity: float = 0.3
+    initial_scale: float = 1.0
+    optim_window_last_n_keyframes: int = 8
+    num_iters_mapping: int = 15
+    num_iters_initialization: int = 400
+    opacity_pruning_threshold: float = 0.2
+    size_pruning_threshold: int = 256
+    ssim_weight: float = 0.2
+    enable_visibility_pruning: bool = False
+    kf_m: float = 0.15
+    kf_cos: float = math.cos(math.pi / 30)
+    n_init_splats: int = 5000               # the literal of Backend.initialize (:626)
+    n_keyframe_splats: int = 100            # the literal of Backend.add_keyframe (:646)
+    sync_every: int = 5                     # `frame.index % 5 == 0` (:871)
+
+
+@dataclass
+class Keyframe:
+    index: int
+    img: Tensor                 # [H,W,3]
+    pose: PoseZhou
+    exposure: Tensor            # [2], fixed once the frame is a keyframe (:660-662)
+    est_depths: Optional[Tensor] = None
+
+
+@dataclass
+class SlamStats:
+    frames: int = 0
+    keyframes: int = 0
+    tracking_evals: int = 0
+    tracking_syncs: int = 0
+    mapping_iters: int = 0
+    inserted: int = 0
+    pruned: int = 0
+    t_tracking: float = 0.0
+    t_mapping: float = 0.0
+    n_splats: int = 0
+    last_tracking_loss: float = float("nan")
+    last_photometric: float = float("nan")
+    history: List[Dict] = field(default_factory=list)
+
+
+class Slam:
+    def __init__(self, camera: Camera, map_conf: Optional[MapConfig] = None,
+                 track_conf: Optional[TrackingConfig] = None, device="cuda", seed: int = 0):
+        self.conf = map_conf or MapConfig()
+        self.camera = camera.to(device)
+        self.dev = torch.device(device)
+        if self.dev.type != "cuda":
+            raise RuntimeError("gslam_b200.slam.Slam needs a CUDA device (no CPU fallback)")
+        self.gen = torch.Generator(device=self.dev).manual_seed(seed)
+        self.tracker = Tracker(self.camera, track_conf, device)
+        c = self.conf
+        self.insertion = InsertFromDepthMap(0.1 * c.initial_scale, 0.2 * c.initial_scale, 0.1,
+                                            c.initial_opacity, False)             # backend.py:139-146
+        self.keyframes: Dict[int, Keyframe] = {}
+        self.frame_poses: List[Tensor] = []          # tracked world->camera matrix of every frame
+        self.last_exposure: Optional[Tensor] = None
+        self.pause_map_optim = False
+        self.total_step = 0
+        self.stats = SlamStats()
+        empty = [torch.zeros((0, w) if w > 1 else (0,), device=self.dev) for w in (3, 4, 3, 1, 3, 1)]
+        self.splats = FlatSplats(empty)
+        # one optimizer, one group per parameter: the reference's six Adam instances (:565-590)
+        self.opt = FusedAdam([{"params": [p], "lr": DEFAULT_LRS[name]}
+                              for p, name in zip(self.splats.params, PARAM_NAMES)])
+        self.pose_opt: Optional[FusedAdam] = None
+        self.step = MappingStep(self.splats, self.opt, ssim_weight=c.ssim_weight,
+                                isotropic_weight=c.isotropic_regularization_weight,
+                                opacity_decay=c.opacity_decay)
+        self.bg1 = torch.zeros(1, 3, device=self.dev)
+
+    # ---- rendering helpers ----------------------------------------------------------------------
+    @torch.no_grad()
+    def render(self, viewmats: Tensor) -> RasterizationOutput:
+        P = self.splats.params
+        C = viewmats.shape[0]
+        Ks = self.camera.intrinsics.expand(C, 3, 3).contiguous()
+        return rasterization(P[0], P[1], P[2], P[3], P[4], viewmats.contiguous(), Ks, self.camera.width,
+                             self.camera.height, packed=False, render_mode="RGB+D", log_uncertainties=P[5],
+                             backgrounds=self.bg1.expand(C, 3).contiguous())
+
+    def _views(self) -> List[KeyframeView]:
+        with torch.no_grad():
+            return [KeyframeView(self.camera.intrinsics, kf.pose(), kf.est_depths)
+                    for kf in self.keyframes.values() if kf.est_depths is not None]
+
+    # ---- backend ---------------------------------------------------------------------------------
+    def initialize(self, img: Tensor) -> None:
+        """Backend.initialize (gslam/backend.py:604-631)."""
+        H, W = self.camera.height, self.camera.width
+        d = self.dev
+        mock_depth = torch.ones(1, H, W, device=d)
+        mock_depth = (mock_depth + (torch.randn(1, H, W, device=d, generator=self.gen) - 0.5) * 0.3) \
+            * self.conf.initial_scale
+        mock_alphas = torch.full((1, H, W, 1), 0.01, device=d)
+        mock = RasterizationOutput(None, mock_alphas, mock_depth)
+        pose = PoseZhou(torch.eye(4, device=d)).to(d)
+        kf = Keyframe(0, img, pose, torch.zeros(2, device=d))
+        self.keyframes[0] = kf
+        self.stats.inserted += self.insertion.step(self.splats, self.opt, mock, self.camera.intrinsics,
+                                                   torch.eye(4, device=d), img, self.conf.n_init_splats,
+                                                   generator=self.gen)
+        self.stats.keyframes = 1
+
+    def add_keyframe(self, index: int, img: Tensor, viewmat: Tensor, exposure: Tensor) -> None:
+        """Backend.add_keyframe (gslam/backend.py:633-679)."""
+        out = self.render(viewmat.view(1, 4, 4))
+        out.depthmaps = out.depthmaps * self.conf.initial_scale
+        self.stats.inserted += self.insertion.step(self.splats, self.opt, out, self.camera.intrinsics, viewmat,
+                                                   img, self.conf.n_keyframe_splats, keyframes=self._views(),
+                                                   generator=self.gen)
+        pose = PoseZhou(viewmat.detach().clone()).to(self.dev)
+        self.keyframes[index] = Keyframe(index, img, pose, exposure.detach().clone(), out.depthmaps[0].clone())
+        group = {"params": [pose.dR, pose.dt], "lr": self.conf.pose_optim_lr}
+        if self.pose_opt is None:
+            self.pose_opt = FusedAdam([group])
+        else:
+            self.pose_opt.add_param_group(group)
+        self.stats.keyframes = len(self.keyframes)
+
+    @torch.no_grad()
+    def to_insert_keyframe(self, viewmat: Tensor) -> bool:
+        """Backend.to_insert_keyframe (gslam/backend.py:741-795): translation against the median
+        rendered depth, then the angle between the optical axes."""
+        prev = self.keyframes[max(self.keyframes)].pose()
+        out = self.render(torch.stack([viewmat, prev]))
+        diff = torch.linalg.inv(viewmat) @ prev
+        translation = diff[:3, 3].norm()
+        seen = out.depthmaps[out.alphas[..., 0] > 0.1]
+        median_depth = seen.median() if seen.numel() else torch.ones((), device=self.dev)
+        cos = torch.nn.functional.cosine_similarity(viewmat[:3, 2], prev[:3, 2], dim=0)
+        decide = torch.stack([translation > self.conf.kf_m * median_depth, cos < self.conf.kf_cos])
+        return bool(decide.any().item())                # ONE host read for both criteria
+
+    def optimization_window(self) -> List[Keyframe]:
+        """Backend.optimization_window (gslam/backend.py:197-246), enable_pgo=False branch: the last n
+        keyframes (the reference's `min(0, ...)` makes the random part empty)."""
+        keys = sorted(self.keyframes)[-self.conf.optim_window_last_n_keyframes:]
+        return [self.keyframes[k] for k in keys]
+
+    def optimize_map(self, n_iters: Optional[int] = None, prune: bool = True, regularize: bool = True) -> None:
+        """Backend.optimize_map (gslam/backend.py:248-409)."""
+        c = self.conf
+        n_iters = c.num_iters_mapping if n_iters is None else n_iters
+        stopper = StopOnPlateau(3, 0.012)
+        self.step.tv_w = c.depth_regularization_weight if regularize else 0.0
+        W, H = self.camera.width, self.camera.height
+        res, window = None, self.optimization_window()
+        gt = torch.stack([k.img for k in window])
+        exposure = torch.stack([k.exposure for k in window])
+        Ks = self.camera.intrinsics.expand(len(window), 3, 3).contiguous()
+        poses = [k.pose for k in window]
+        for _ in range(n_iters):
+            self.total_step += 1
+            for p in poses:
+                p.dR.grad = None
+                p.dt.grad = None
+            res = self.step(pose_batch(poses), Ks, gt, exposure, W, H, len(window))
+            if self.pose_opt is not None:
+                self.pose_opt.step()            # keyframe 0 is in no group: its pose stays fixed (:604-611)
+            self.stats.mapping_iters += 1
+            photo = float(res.photometric)      # the reference's per-iteration .item() (:338-349)
+            self.stats.last_photometric = photo
+            if stopper.stop(photo):
+                self.pause_map_optim = True
+                break
+        if res is None:
+            return
+        with torch.no_grad():
+            for k, dmap in zip(window, res.outputs.depthmaps):
+                k.est_depths = dmap.detach().clone()
+            if prune:
+                self.stats.pruned += prune_round(
+                    self.splats, self.opt, res.radii, res.n_touched, c.opacity_pruning_threshold,
+                    c.size_pruning_threshold, 3 if c.enable_visibility_pruning else None,
+                    c.optim_window_last_n_keyframes)
+        self.stats.n_splats = self.splats.n
+
+    def sync(self) -> None:
+        """Backend.sync -> Frontend.sync (backend.py:508-519, frontend.py:254-269)."""
+        P = [p.detach() for p in self.splats.params]
+        ages = torch.zeros(self.splats.n, dtype=torch.long, device=self.dev)
+        self.tracker.set_map(GaussianSplattingData(P[0], P[1], P[2], P[3], P[4], P[5], ages))
+
+    # ---- one frame --------------------------------------------------------------------------------
+    def process_frame(self, img: Tensor, idle_rounds: int = 1) -> Tensor:
+        """Track `img` [H,W,3] (device, values in [0,1]) and let the backend work; returns the frame's
+        world->camera matrix."""
+        idx = self.stats.frames
+        sync = torch.cuda.synchronize
+        if idx == 0:
+            t0 = time.perf_counter()
+            self.initialize(img)
+            self.pause_map_optim = False
+            self.optimize_map(self.conf.num_iters_initialization, prune=False, regularize=True)
+            self.sync()
+            sync()
+            self.stats.t_mapping += time.perf_counter() - t0
+            viewmat = torch.eye(4, device=self.dev)
+            self.last_exposure = torch.zeros(2, device=self.dev)
+        else:
+            t0 = time.perf_counter()
+            prev2 = self.frame_poses[-2] if len(self.frame_poses) > 1 else None
+            init = constant_motion(prev2, self.frame_poses[-1])
+            r = self.tracker.track_lbfgs(img, init, self.last_exposure)
+            viewmat, self.last_exposure = r.viewmat, r.exposure
+            self.stats.tracking_evals += r.n_evals
+            self.stats.tracking_syncs += r.n_syncs
+            self.stats.last_tracking_loss = r.loss
+            sync()
+            t1 = time.perf_counter()
+            self.stats.t_tracking += t1 - t0
+            if self.to_insert_keyframe(viewmat):
+                self.pause_map_optim = False
+                self.add_keyframe(idx, img, viewmat, r.exposure)
+                self.optimize_map(1, prune=True, regularize=False)
+            for _ in range(idle_rounds):
+                if self.pause_map_optim:
+                    break
+                self.optimize_map()
+            if idx % self.conf.sync_every == 0:
+                self.sync()
+            sync()
+            self.stats.t_mapping += time.perf_counter() - t1
+        self.frame_poses.append(viewmat)
+        self.stats.frames += 1
+        self.stats.n_splats = self.splats.n
+        return viewmat
+
+
+@torch.no_grad()
+def synthetic_sequence(n_frames: int, n_gauss: int = 20000, scale: float = 1.0, device="cuda", seed: int = 0):
+    """(camera, images [F,H,W,3], gt viewmats [F,4,4]): renders of a random `synthetic.make_scene` map
+    along `synthetic.smooth_trajectory`, produced by this package's own rasterizer (the data of cfg5)."""
+    from .synthetic import make_scene, smooth_trajectory
+    sc = make_scene(n_gauss, 1, "tum", scale, seed=seed).to(device)
+    cam = Camera(sc.Ks[0].clone(), sc.height, sc.width)
+    poses = smooth_trajectory(n_frames).to(device)
+    imgs = []
+    P = sc.params()
+    for i in range(0, n_frames, 8):
+        vm = poses[i:i + 8].contiguous()
+        C = vm.shape[0]
+        out = rasterization(P[0], P[1], P[2], P[3], P[4], vm, sc.Ks[0].expand(C, 3, 3).contiguous(), sc.width,
+                            sc.height, packed=False, render_mode="RGB+D", log_uncertainties=P[5],
+                            backgrounds=torch.full((C, 3), 0.5, device=device))
+        imgs.append(out.rgbs.clamp(0, 1).clone())
+    return cam, torch.cat(imgs), poses
+
+
+def run_sequence(n_frames: int, n_gauss: int = 20000, scale: float = 1.0, device="cuda", seed: int = 0,
+                 map_conf: Optional[MapConfig] = None, track_conf: Optional[TrackingConfig] = None,
+                 idle_rounds: int = 1):
+    """cfg5: the whole loop over a synthetic sequence -> (Slam, frames/s, gt viewmats)."""
+    cam, imgs, gt_poses = synthetic_sequence(n_frames, n_gauss, scale, device, seed)
+    slam = Slam(cam, map_conf, track_conf, device, seed)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for i in range(n_frames):
+        slam.process_frame(imgs[i], idle_rounds)
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    return slam, n_frames / dt, gt_poses

@@ -107,3 +107,21 @@ def target_images(n_views: int, height: int, width: int, seed: int = 2) -> torch
     low = torch.rand(n_views, 3, max(height // 16, 2), max(width // 16, 2), generator=g)
     img = torch.nn.functional.interpolate(low, size=(height, width), mode="bilinear", align_corners=False)
     return img.permute(0, 2, 3, 1).contiguous().clamp(0, 1)
+
+
+def smooth_trajectory(n_frames: int, amp_t: float = 0.25, amp_deg: float = 6.0, period: int = 240) -> torch.Tensor:
+    """World->camera matrices [F,4,4] of a hand-held-like sweep that starts at identity: sinusoidal
+    sideways / vertical translation (amplitude `amp_t` metres) and yaw / pitch (amplitude `amp_deg`),
+    at most a few millimetres and a tenth of a degree per frame (the cfg5 sequence)."""
+    out = []
+    for i in range(n_frames):
+        ph = 2 * math.pi * i / period
+        yaw = math.radians(amp_deg) * math.sin(ph)
+        pitch = math.radians(amp_deg) * 0.5 * (1 - math.cos(ph))
+        Ry = torch.tensor([[math.cos(yaw), 0, math.sin(yaw)], [0, 1, 0], [-math.sin(yaw), 0, math.cos(yaw)]])
+        Rx = torch.tensor([[1, 0, 0], [0, math.cos(pitch), -math.sin(pitch)], [0, math.sin(pitch), math.cos(pitch)]])
+        T = torch.eye(4)
+        T[:3, :3] = Rx @ Ry
+        T[:3, 3] = torch.tensor([amp_t * math.sin(ph), 0.4 * amp_t * (1 - math.cos(ph)), 0.1 * amp_t * math.sin(2 * ph)])
+        out.append(T)
+    return torch.stack(out)

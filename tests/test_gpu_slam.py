@@ -1,0 +1,37 @@
+"""cfg5 at test size: the tracking + mapping + insertion / pruning loop over a short synthetic
+sequence (gslam_b200.slam, following main.py / Frontend.run / Backend.run of the reference)."""
+import pytest
+import torch
+
+from gslam_b200.slam import MapConfig, run_sequence
+from gslam_b200.tracking import TrackingConfig
+
+pytestmark = pytest.mark.gpu
+
+
+def test_short_sequence_runs_every_stage(cuda):
+    conf = MapConfig(num_iters_initialization=80, num_iters_mapping=5, kf_m=0.02)
+    slam, fps, gt_poses = run_sequence(14, n_gauss=6_000, scale=0.5, device=cuda, map_conf=conf,
+                                       track_conf=TrackingConfig(lbfgs_max_iter=8))
+    st = slam.stats
+    assert st.frames == 14 and fps > 0
+    assert st.inserted >= conf.n_init_splats * 0.9 and st.n_splats == slam.splats.n > 0
+    assert st.keyframes >= 2                              # kf_m lowered so the sweep triggers insertion
+    assert st.mapping_iters >= 80 and st.tracking_evals >= 13 * 10
+    assert st.tracking_syncs < st.tracking_evals          # the Adam phase is sync-free
+    poses = torch.stack(slam.frame_poses)
+    assert torch.isfinite(poses).all()
+    R = poses[:, :3, :3]
+    assert torch.allclose(R @ R.transpose(1, 2), torch.eye(3, device=cuda).expand_as(R), atol=1e-4)
+    assert torch.allclose(poses[:, 3], torch.tensor([0.0, 0, 0, 1], device=cuda).expand(14, 4))
+    # the map explains the first frame better than a flat image does
+    out = slam.render(torch.eye(4, device=cuda).view(1, 4, 4))
+    img0 = slam.keyframes[0].img
+    err_map = (out.rgbs[0] - img0).abs().mean()
+    err_flat = (img0.mean(dim=(0, 1), keepdim=True) - img0).abs().mean()
+    assert err_map < err_flat, (float(err_map), float(err_flat))
+    for p in slam.splats.params:
+        assert torch.isfinite(p).all()
+    # Adam state follows the parameters through insertion and pruning
+    for p in slam.splats.params:
+        assert slam.opt.state[p]["exp_avg"].shape == p.shape
