@@ -20,6 +20,7 @@ optional `torch.Generator` so that tests are repeatable.
 """
 from __future__ import annotations
 
+import math
 from dataclasses import dataclass
 from typing import Dict, List, Optional, Sequence
 
@@ -156,3 +157,58 @@ class InsertFromDepthMap:
         if not bool(keep.all()):
             new_params = {k: v[keep] for k, v in new_params.items()}
         return add_new_splats(splats, optimizer, new_params)
+
+
+class InsertUsingImagePlaneGradients:
+    """The 3DGS densification rule of reference gslam/insertion.py:276-347 on the flat layout.
+
+    A splat whose image-plane gradient norm (averaged over the window's views, scaled by half the
+    image size times the view count, :300-309) exceeds `grow_grad2d` is DUPLICATED when its largest
+    scale is at most `grow_scale3d` and SPLIT otherwise: the split copy is displaced by
+    `covar @ N(0, I)` and shrunk by 1/1.6 (:80-97).  Copies start with log-uncertainty 1 and zero
+    Adam moments; the originals stay (as in the reference).  Both sets are appended in ONE surgery
+    launch (the reference runs `_add_new_splats` twice, each a `cat` per tensor and per moment).
+    """
+
+    def __init__(self, grow_grad2d: float, grow_scale3d: float):
+        self.grow_grad2d = grow_grad2d
+        self.grow_scale3d = grow_scale3d
+
+    @torch.no_grad()
+    def masks(self, means2d_grad: Tensor, log_scales: Tensor, width: int, height: int, n_cameras: int):
+        """(to_duplicate, to_split) [N] from means2d.grad [C,N,2]."""
+        g = means2d_grad * means2d_grad.new_tensor([width / 2.0 * n_cameras, height / 2.0 * n_cameras])
+        high = g.norm(dim=-1).mean(dim=0) > self.grow_grad2d
+        small = torch.exp(log_scales).max(dim=-1).values <= self.grow_scale3d
+        return high & small, high & ~small
+
+    @torch.no_grad()
+    def step(self, splats: FlatSplats, optimizer, rasterization_output: RasterizationOutput,
+             generator: Optional[torch.Generator] = None):
+        """Returns (num_duplicate, num_split); `rasterization_output.means2d.grad` must be populated
+        (`out.means2d.retain_grad()` before backward, gslam/backend.py:326)."""
+        from .rasterization import quat_scale_to_covar_preci
+        from .mapping import PARAM_NAMES
+        out = rasterization_output
+        grad = out.means2d.grad
+        if grad is None:
+            raise RuntimeError("InsertUsingImagePlaneGradients: means2d.grad is empty (call retain_grad())")
+        P = {name: p.detach() for name, p in zip(PARAM_NAMES, splats.params)}
+        dup, split = self.masks(grad, P["scales"], out.width, out.height, out.n_cameras)
+        both = torch.cat([torch.nonzero(dup).reshape(-1), torch.nonzero(split).reshape(-1)])
+        n_dup = int(dup.sum().item())                      # the reference reads both counts too (:318-319)
+        n_split = both.numel() - n_dup
+        if both.numel() == 0:
+            return 0, 0
+        new = {name: p[both].clone() for name, p in P.items()}
+        if n_split:
+            covars, _ = quat_scale_to_covar_preci(new["quats"][n_dup:], torch.exp(new["scales"][n_dup:]),
+                                                  compute_preci=False)
+            noise = torch.randn(n_split, 3, device=covars.device, generator=generator)
+            new["means"][n_dup:] += torch.einsum("bij,bj->bi", covars, noise)
+            new["scales"][n_dup:] -= math.log(1.6)
+        new["log_uncertainties"].fill_(1.0)
+        add_new_splats(splats, optimizer, new)
+        if out.radii is not None:
+            out.radii = torch.cat([out.radii, out.radii.new_zeros(out.radii.shape[0], both.numel())], dim=1)
+        return n_dup, n_split

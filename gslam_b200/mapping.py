@@ -153,6 +153,7 @@ class MappingStep:
         self.render_fn, self.loss_fn = render_fn, loss_fn
         self.ssim_weight, self.iso_w, self.decay, self.group = ssim_weight, isotropic_weight, opacity_decay, group
         self.tv_w = depth_tv_weight
+        self.retain_means2d_grad = False      # out.means2d.retain_grad() of gslam/backend.py:326 (densification)
 
     def __call__(self, viewmats: Tensor, Ks: Tensor, gt_imgs: Tensor, exposure: Optional[Tensor],
                  width: int, height: int, n_views_total: int, background: Optional[Tensor] = None,
@@ -174,6 +175,8 @@ class MappingStep:
         from . import ops
         n = self.splats.n
         ops.grad_tail_floats = n + 2          # room behind the flat gradient for counts and loss scalars
+        if self.retain_means2d_grad:
+            out.means2d.retain_grad()
         try:
             loss.backward()
         finally:

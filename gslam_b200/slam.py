@@ -11,7 +11,8 @@ is kept is the ORDER OF WORK on the render path, executed inline on one CUDA str
     frame i > 0  Frontend.track (frontend.py:170-247): constant-motion start, igs_track_lbfgs
                  Backend, ADD_FRAME (:856-873): to_insert_keyframe (:741-795) -> add_keyframe
                  (:633-679) -> optimize_map(1, prune=True, regularize=False); sync every 5th frame
-                 Backend, idle (:846-852): optimize_map() [+ run_pruning] until StopOnPlateau pauses it
+                 Backend, idle (:846-852): optimize_map(), run_pruning(), optimize_poses_lbfgs() until
+                 StopOnPlateau pauses it
 
 Every step is the corresponding module of this package: `tracking.Tracker` (CUDA-graph closure),
 `mapping.MappingStep` (flat [15 N] layout, fused losses, one-launch Adam), `insertion.
@@ -20,8 +21,7 @@ hand-off of `Backend.sync` -> `Frontend.sync` (deepcopy + pickle through an mp.Q
 reference, backend.py:508-519) is one device-to-device copy of the flat parameter buffer
 (`Tracker.set_map`).
 
-Not reproduced: `InsertUsingImagePlaneGradients` (every 200th step, :328-336), the pose-graph /
-loop-closure bookkeeping (`enable_pgo`, off by default) and `optimize_poses_lbfgs` (:436-506).
+Not reproduced: the pose-graph / loop-closure bookkeeping (`enable_pgo`, off by default).
 """
 from __future__ import annotations
 
@@ -30,10 +30,13 @@ import time
 from dataclasses import dataclass, field
 from typing import Dict, List, Optional
 
+import numpy as np
 import torch
 from torch import Tensor
 
-from .insertion import InsertFromDepthMap, KeyframeView
+from .lbfgs import lbfgs_minimize
+from .losses import photometric_ssim_loss
+from .insertion import InsertFromDepthMap, InsertUsingImagePlaneGradients, KeyframeView
 from .map import GaussianSplattingData
 from .mapping import DEFAULT_LRS, PARAM_NAMES, FlatSplats, MappingStep
 from .optim import FusedAdam
@@ -64,6 +67,10 @@ class MapConfig:
     n_init_splats: int = 5000               # the literal of Backend.initialize (:626)
     n_keyframe_splats: int = 100            # the literal of Backend.add_keyframe (:646)
     sync_every: int = 5                     # `frame.index % 5 == 0` (:871)
+    densify_every: int = 200                # `(self.total_step % 200) == 0` (:328)
+    grow_grad2d: float = 0.0002             # InsertUsingImagePlaneGradients(0.0002, 0.01) (:147-150)
+    grow_scale3d: float = 0.01
+    optimize_poses: bool = True             # optimize_poses_lbfgs after every idle mapping round (:851)
 
 
 @dataclass
@@ -84,6 +91,8 @@ class SlamStats:
     mapping_iters: int = 0
     inserted: int = 0
     pruned: int = 0
+    densified: int = 0
+    pose_lbfgs_evals: int = 0
     t_tracking: float = 0.0
     t_mapping: float = 0.0
     n_splats: int = 0
@@ -105,6 +114,7 @@ class Slam:
         c = self.conf
         self.insertion = InsertFromDepthMap(0.1 * c.initial_scale, 0.2 * c.initial_scale, 0.1,
                                             c.initial_opacity, False)             # backend.py:139-146
+        self.insertion_3dgs = InsertUsingImagePlaneGradients(c.grow_grad2d, c.grow_scale3d)
         self.keyframes: Dict[int, Keyframe] = {}
         self.frame_poses: List[Tensor] = []          # tracked world->camera matrix of every frame
         self.last_exposure: Optional[Tensor] = None
@@ -208,7 +218,27 @@ class Slam:
             for p in poses:
                 p.dR.grad = None
                 p.dt.grad = None
-            res = self.step(pose_batch(poses), Ks, gt, exposure, W, H, len(window))
+            densify = c.densify_every > 0 and self.total_step % c.densify_every == 0
+            self.step.retain_means2d_grad = densify
+            res = self.step(pose_batch(poses), Ks, gt, exposure, W, H, len(window), step_optimizer=not densify)
+            if densify:
+                # the reference densifies between backward and the optimizer step (:328-351): the
+                # parameters it re-creates carry no gradient, so that iteration takes no splat step and
+                # only the opacity decay applies (radii padded with zeros for the new rows)
+                n_dup, n_split = self.insertion_3dgs.step(self.splats, self.opt, res.outputs, self.gen)
+                self.stats.inserted += n_dup + n_split
+                self.stats.densified += n_dup + n_split
+                prune = False
+                if n_dup + n_split:
+                    with torch.no_grad():
+                        seen_twice = (res.outputs.radii > 0).sum(dim=0) > 1
+                        opac = self.splats.params[3]
+                        opac.mul_(torch.where(seen_twice, c.opacity_decay, 1.0))
+                        res.radii = res.outputs.radii
+                        res.n_touched = torch.cat([res.n_touched, res.n_touched.new_zeros(
+                            res.n_touched.shape[0], n_dup + n_split)], dim=1)
+                else:
+                    self.opt.step(decay_param=self.splats.params[3], vis_count=res.vis_count, decay=c.opacity_decay)
             if self.pose_opt is not None:
                 self.pose_opt.step()            # keyframe 0 is in no group: its pose stays fixed (:604-611)
             self.stats.mapping_iters += 1
@@ -228,6 +258,66 @@ class Slam:
                     c.size_pruning_threshold, 3 if c.enable_visibility_pruning else None,
                     c.optim_window_last_n_keyframes)
         self.stats.n_splats = self.splats.n
+
+    @torch.no_grad()
+    def run_pruning(self) -> None:
+        """Backend.run_pruning (gslam/backend.py:411-434): size and opacity criteria seen from the
+        latest keyframe."""
+        last = self.keyframes[max(self.keyframes)]
+        out = self.render(last.pose().view(1, 4, 4))
+        c = self.conf
+        self.stats.pruned += prune_round(self.splats, self.opt, out.radii, out.n_touched,
+                                         c.opacity_pruning_threshold, c.size_pruning_threshold, None,
+                                         c.optim_window_last_n_keyframes)
+        self.stats.n_splats = self.splats.n
+
+    def optimize_poses_lbfgs(self) -> Optional[float]:
+        """Backend.optimize_poses_lbfgs (gslam/backend.py:436-506): L-BFGS (history 10, strong Wolfe,
+        tolerance_change 1e-7, lr 1) over the window's poses except keyframe 0, objective = the
+        photometric part of the mapping loss on the frozen map.  The 9 W unknowns live on the host
+        (gslam_b200.lbfgs); an evaluation is one upload, one render + loss + backward to the poses
+        (no gradient to the map, which the reference computes and discards) and one download."""
+        window = self.optimization_window()
+        free = [k for k in window if k.index != 0]
+        if not free:
+            return None
+        W, H = self.camera.width, self.camera.height
+        gt = torch.stack([k.img for k in window])
+        exposure = torch.stack([k.exposure for k in window])
+        Ks = self.camera.intrinsics.expand(len(window), 3, 3).contiguous()
+        poses = [k.pose for k in window]
+        P = [p.detach() for p in self.splats.params]
+        bg = self.bg1.expand(len(window), 3).contiguous()
+        with torch.no_grad():
+            x0 = torch.cat([torch.cat([k.pose.dR, k.pose.dt]) for k in free]).cpu().numpy()
+
+        def scatter(x) -> None:
+            th = torch.from_numpy(np.asarray(x, dtype=np.float32)).to(self.dev)
+            with torch.no_grad():
+                for i, k in enumerate(free):
+                    k.pose.dR.copy_(th[9 * i:9 * i + 6])
+                    k.pose.dt.copy_(th[9 * i + 6:9 * i + 9])
+
+        def evaluate(x):
+            scatter(x)
+            for k in free:
+                k.pose.dR.grad = None
+                k.pose.dt.grad = None
+            out = rasterization(P[0], P[1], P[2], P[3], P[4], pose_batch(poses), Ks, W, H, packed=False,
+                                render_mode="RGB+D", log_uncertainties=P[5], backgrounds=bg)
+            total, _ = photometric_ssim_loss(out.render, gt, exposure, 0.0, "mapping")
+            total.backward()
+            packed = torch.cat([total.detach().view(1)] + [t for k in free for t in (k.pose.dR.grad, k.pose.dt.grad)])
+            r = packed.cpu().numpy()                       # the evaluation's one sync
+            self.stats.pose_lbfgs_evals += 1
+            return float(r[0]), r[1:]
+
+        res = lbfgs_minimize(evaluate, x0, lr=1.0, max_iter=20, tolerance_change=1e-7, history_size=10)
+        scatter(res.x)
+        for k in free:
+            k.pose.dR.grad = None
+            k.pose.dt.grad = None
+        return res.last_loss
 
     def sync(self) -> None:
         """Backend.sync -> Frontend.sync (backend.py:508-519, frontend.py:254-269)."""
@@ -267,10 +357,14 @@ class Slam:
                 self.pause_map_optim = False
                 self.add_keyframe(idx, img, viewmat, r.exposure)
                 self.optimize_map(1, prune=True, regularize=False)
-            for _ in range(idle_rounds):
+            for _ in range(idle_rounds):                  # Backend.run with an empty queue (:846-852)
                 if self.pause_map_optim:
                     break
                 self.optimize_map()
+                if len(self.keyframes) > 1:
+                    self.run_pruning()
+                    if self.conf.optimize_poses:
+                        self.optimize_poses_lbfgs()
             if idx % self.conf.sync_every == 0:
                 self.sync()
             sync()

@@ -94,3 +94,71 @@ def test_occlusion_filter_against_earlier_keyframes(cuda):
     vm = sc.viewmats[1]
     z1 = (cand["means"] @ vm[:3, :3].t() + vm[:3, 3])[:, 2]
     assert bool((z1[~keep] < 1.0).all())
+
+
+def test_first_insertion_into_an_empty_map_uses_neighbour_distances(cuda):
+    # Backend.initialize (gslam/backend.py:604-631): no map yet, mock depth, 3-NN scales (:226-231)
+    from gslam_b200.insertion import knn_mean_distance
+    sc = make_scene(10, 1, "tum", 0.5).to(cuda)
+    empty = [torch.zeros((0, w) if w > 1 else (0,), device=cuda) for w in (3, 4, 3, 1, 3, 1)]
+    splats = FlatSplats(empty)
+    opt = FusedAdam([dict(params=[p], lr=DEFAULT_LRS[nm]) for p, nm in zip(splats.params, PARAM_NAMES)])
+    H, W = sc.height, sc.width
+    from gslam_b200.rasterization import RasterizationOutput
+    mock = RasterizationOutput(None, torch.full((1, H, W, 1), 0.01, device=cuda),
+                               1.0 + 0.1 * torch.randn(1, H, W, device=cuda))
+    img = target_images(1, H, W)[0].to(cuda)
+    ins = InsertFromDepthMap(0.1, 0.2, 0.1, 0.3, False)
+    added = ins.step(splats, opt, mock, sc.Ks[0], torch.eye(4, device=cuda), img, 500,
+                     generator=torch.Generator(device=cuda).manual_seed(3))
+    assert added == 500 == splats.n
+    means, scales = splats.params[0].detach(), torch.exp(splats.params[2].detach())
+    d = torch.cdist(means, means)
+    ref = d.topk(4, largest=False).values[:, 1:].mean(dim=1)
+    assert torch.allclose(knn_mean_distance(means, 3), ref, rtol=1e-5, atol=1e-7)
+    assert torch.allclose(scales, ref.clamp_min(1e-6)[:, None].expand(500, 3), rtol=1e-4)
+    assert knn_mean_distance(means, 3, chunk=128).allclose(ref, rtol=1e-5, atol=1e-7)
+
+
+def test_image_plane_gradient_densification(cuda):
+    # InsertUsingImagePlaneGradients (gslam/insertion.py:276-347): duplicate small, split large
+    from gslam_b200.insertion import InsertUsingImagePlaneGradients
+    sc, splats, opt, _ = _world(cuda, n=5000, views=2)
+    n0 = splats.n
+    P = splats.params
+    out = rasterization(*P[:5], sc.viewmats, sc.Ks, sc.width, sc.height, packed=False, render_mode="RGB+D",
+                        log_uncertainties=P[5], backgrounds=torch.zeros(2, 3, device=cuda))
+    out.means2d.retain_grad()
+    gt = target_images(2, sc.height, sc.width).to(cuda)
+    (out.rgbs - gt).square().mean().backward()
+    grad = out.means2d.grad
+    assert grad is not None and grad.shape == (2, n0, 2)
+    g = grad.clone()
+    g[..., 0] *= sc.width / 2.0 * 2
+    g[..., 1] *= sc.height / 2.0 * 2
+    score = g.norm(dim=-1).mean(dim=0)
+    thr = float(score.quantile(0.9))                      # densify the top 10 %
+    scale_thr = float(torch.exp(P[2].detach()).max(dim=-1).values.median())
+    high = score > thr
+    small = torch.exp(P[2].detach()).max(dim=-1).values <= scale_thr
+    dup_ids, split_ids = torch.nonzero(high & small).reshape(-1), torch.nonzero(high & ~small).reshape(-1)
+    before = [p.detach().clone() for p in P]
+    ins = InsertUsingImagePlaneGradients(thr, scale_thr)
+    n_dup, n_split = ins.step(splats, opt, out, generator=torch.Generator(device=cuda).manual_seed(5))
+    assert (n_dup, n_split) == (dup_ids.numel(), split_ids.numel()) and n_dup > 0 and n_split > 0
+    assert splats.n == n0 + n_dup + n_split
+    new = [p.detach() for p in splats.params]
+    for k in range(6):
+        assert torch.equal(new[k][:n0], before[k])                       # originals stay
+    for k in (0, 1, 2, 3, 4):                                             # duplicates are copies
+        assert torch.equal(new[k][n0:n0 + n_dup], before[k][dup_ids])
+    assert torch.equal(new[5][n0:], torch.ones(n_dup + n_split, device=cuda))
+    for k in (1, 3, 4):                                                   # split: same shape parameters ...
+        assert torch.equal(new[k][n0 + n_dup:], before[k][split_ids])
+    assert torch.allclose(new[2][n0 + n_dup:], before[2][split_ids] - math.log(1.6), atol=1e-6)
+    moved = (new[0][n0 + n_dup:] - before[0][split_ids]).norm(dim=1)
+    assert float(moved.max()) > 0 and float(moved.median()) < float(torch.exp(before[2][split_ids]).max()) ** 2 * 10
+    assert out.radii.shape == (2, splats.n) and int(out.radii[:, n0:].abs().sum()) == 0
+    for p in splats.params:
+        st = opt.state[p]
+        assert bool((st["exp_avg"][n0:] == 0).all()) and st["exp_avg"].shape == p.shape

@@ -35,3 +35,24 @@ def test_short_sequence_runs_every_stage(cuda):
     # Adam state follows the parameters through insertion and pruning
     for p in slam.splats.params:
         assert slam.opt.state[p]["exp_avg"].shape == p.shape
+
+
+def test_window_pose_lbfgs_moves_only_the_free_keyframes(cuda):
+    from gslam_b200.slam import Slam, synthetic_sequence
+    cam, imgs, gt_poses = synthetic_sequence(12, 6_000, 0.5, cuda)
+    slam = Slam(cam, MapConfig(num_iters_initialization=60), TrackingConfig(lbfgs_max_iter=4), cuda)
+    slam.process_frame(imgs[0])
+    # a second keyframe whose pose starts a little off the tracked one
+    r = slam.tracker.track_lbfgs(imgs[8], torch.eye(4, device=cuda))
+    slam.add_keyframe(8, imgs[8], r.viewmat, r.exposure)
+    slam.optimize_map(3, prune=False, regularize=False)
+    before = slam.keyframes[8].pose().detach().clone()
+    loss = slam.optimize_poses_lbfgs()
+    assert loss is not None and loss == loss and slam.stats.pose_lbfgs_evals >= 2
+    after = slam.keyframes[8].pose().detach()
+    assert torch.isfinite(after).all() and not torch.equal(before, after)
+    assert torch.equal(slam.keyframes[0].pose().detach(), torch.eye(4, device=cuda))   # index 0 is fixed
+    assert slam.keyframes[8].pose.dR.grad is None
+    n0 = slam.splats.n
+    slam.run_pruning()
+    assert slam.splats.n <= n0
