@@ -84,6 +84,18 @@ def pose_batch(poses: List[PoseZhou]) -> Tensor:
                       torch.stack([p.dt for p in poses]))
 
 
+def rigid_inverse(T: Tensor) -> Tensor:
+    """Inverse of a rigid [4,4] (or [...,4,4]) transform, [R^T | -R^T t]: what `torch.linalg.inv`
+    returns for the view matrices of this path (rotation from Gram-Schmidt, gslam/primitives.py:
+    15-36) without the LU factorisation, its pivoting sync and the ~170 ms solver start-up."""
+    Rt = T[..., :3, :3].transpose(-1, -2)
+    out = torch.zeros_like(T)
+    out[..., :3, :3] = Rt
+    out[..., :3, 3] = -(Rt @ T[..., :3, 3:4])[..., 0]
+    out[..., 3, 3] = 1.0
+    return out
+
+
 @dataclass
 class Camera:
     """The fields of the reference Camera (gslam/primitives.py:350-367) that the render path reads."""

@@ -43,7 +43,7 @@ from .optim import FusedAdam
 from .primitives import Camera, PoseZhou, pose_batch
 from .pruning import prune_round
 from .rasterization import RasterizationOutput, rasterization
-from .tracking import StopOnPlateau, Tracker, TrackingConfig, constant_motion
+from .tracking import StopOnPlateau, Tracker, TrackingConfig, constant_motion, rigid_inverse
 
 
 @dataclass
@@ -98,6 +98,7 @@ class SlamStats:
     n_splats: int = 0
     last_tracking_loss: float = float("nan")
     last_photometric: float = float("nan")
+    first_photometric: float = float("nan")
     history: List[Dict] = field(default_factory=list)
 
 
@@ -187,7 +188,7 @@ class Slam:
         rendered depth, then the angle between the optical axes."""
         prev = self.keyframes[max(self.keyframes)].pose()
         out = self.render(torch.stack([viewmat, prev]))
-        diff = torch.linalg.inv(viewmat) @ prev
+        diff = rigid_inverse(viewmat) @ prev
         translation = diff[:3, 3].norm()
         seen = out.depthmaps[out.alphas[..., 0] > 0.1]
         median_depth = seen.median() if seen.numel() else torch.ones((), device=self.dev)
@@ -244,6 +245,8 @@ class Slam:
             self.stats.mapping_iters += 1
             photo = float(res.photometric)      # the reference's per-iteration .item() (:338-349)
             self.stats.last_photometric = photo
+            if self.stats.mapping_iters == 1:
+                self.stats.first_photometric = photo
             if stopper.stop(photo):
                 self.pause_map_optim = True
                 break

@@ -32,6 +32,7 @@ CUDA only: there is no CPU path (the closure is the sm_100a render path).
 """
 from __future__ import annotations
 
+import math
 from dataclasses import dataclass
 from typing import List, Optional
 
@@ -42,7 +43,7 @@ from .graph import GraphedStep
 from .lbfgs import lbfgs_minimize
 from .losses import tracking_loss
 from .map import GaussianSplattingData
-from .primitives import Camera, pose_chain
+from .primitives import Camera, pose_chain, rigid_inverse  # noqa: F401  (re-exported)
 
 N_POSE = 9          # dR[6] | dt[3]
 N_THETA = 11        # ... | exposure (a, b)
@@ -147,6 +148,8 @@ class Tracker:
         lr_sgd[N_POSE:] = self.conf.exposure_lr
         self.lr_sgd = lr_sgd * mask
         self.splats: Optional[GaussianSplattingData] = None
+        self.capacity = 0
+        self.n_live = 0
         self._graphs = {}
         self.headroom = 1.5          # capacity of the captured key buffers over the measured count
         self.n_evals = 0
@@ -154,10 +157,36 @@ class Tracker:
 
     # ---- the map -------------------------------------------------------------------------------
     def set_map(self, splats: GaussianSplattingData) -> None:
-        """Frontend.sync (gslam/frontend.py:254-269): a frozen copy of the backend's map.  The
-        captured graphs bake in the parameter pointers and N, so they are dropped here."""
-        self.splats = splats.no_grad_clone()
-        self._graphs = {}
+        """Frontend.sync (gslam/frontend.py:254-269): a frozen copy of the backend's map.
+
+        The captured graphs bake in the parameter pointers and the Gaussian count, and the map grows
+        and shrinks between syncs.  So the copy goes into buffers of fixed CAPACITY (1.25 x the count,
+        rounded up to 1024 rows): rows [0, N) hold the map, the rest are "dead" rows parked 1e15 m
+        away, which the projection culls against the far plane (radius 0, no tile, no pixel), so the
+        render is that of the N-row map.  A sync is then one device-to-device copy and the graphs
+        survive it; only a map that outgrows the capacity allocates anew and drops them."""
+        src = [getattr(splats, name).detach() for name in GaussianSplattingData._per_splat_params[:6]]
+        n = src[0].shape[0]
+        if self.splats is None or n > self.capacity:
+            self.capacity = max(1024, -(-int(n * 1.25) // 1024) * 1024)
+            d, cap = self.dev, self.capacity
+            self.splats = GaussianSplattingData(
+                torch.empty(cap, 3, device=d), torch.empty(cap, 4, device=d), torch.empty(cap, 3, device=d),
+                torch.empty(cap, device=d), torch.empty(cap, 3, device=d), torch.empty(cap, device=d),
+                torch.zeros(cap, dtype=torch.long, device=d)).to(d)
+            for name in GaussianSplattingData._per_splat_params:
+                getattr(self.splats, name).requires_grad_(False)
+            self._graphs = {}
+        dst = [getattr(self.splats, name) for name in GaussianSplattingData._per_splat_params[:6]]
+        dead = (1e15, None, math.log(1e-3), -20.0, 0.0, 0.0)
+        with torch.no_grad():
+            for k, (t, v) in enumerate(zip(dst, dead)):
+                t[:n].copy_(src[k])
+                if k == 1:
+                    t[n:] = t.new_tensor([1.0, 0.0, 0.0, 0.0])
+                else:
+                    t[n:] = v
+        self.n_live = n
 
     # ---- the objective -------------------------------------------------------------------------
     def _evaluate(self) -> Tensor:
@@ -356,4 +385,4 @@ def constant_motion(prev2: Optional[Tensor], prev1: Tensor) -> Tensor:
     """Initial pose of a new frame (gslam/frontend.py:176-183): pose_b @ inv(pose_a) @ pose_b."""
     if prev2 is None:
         return prev1.clone()
-    return prev1 @ torch.linalg.inv(prev2) @ prev1
+    return prev1 @ rigid_inverse(prev2) @ prev1

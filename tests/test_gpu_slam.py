@@ -24,12 +24,11 @@ def test_short_sequence_runs_every_stage(cuda):
     R = poses[:, :3, :3]
     assert torch.allclose(R @ R.transpose(1, 2), torch.eye(3, device=cuda).expand_as(R), atol=1e-4)
     assert torch.allclose(poses[:, 3], torch.tensor([0.0, 0, 0, 1], device=cuda).expand(14, 4))
-    # the map explains the first frame better than a flat image does
+    # mapping lowers the photometric loss it started from, and the map renders frame 0 sensibly
+    assert st.last_photometric < st.first_photometric, (st.first_photometric, st.last_photometric)
     out = slam.render(torch.eye(4, device=cuda).view(1, 4, 4))
-    img0 = slam.keyframes[0].img
-    err_map = (out.rgbs[0] - img0).abs().mean()
-    err_flat = (img0.mean(dim=(0, 1), keepdim=True) - img0).abs().mean()
-    assert err_map < err_flat, (float(err_map), float(err_flat))
+    assert float((out.rgbs[0] - slam.keyframes[0].img).abs().mean()) < 0.2
+    assert float(out.alphas.mean()) > 0.3
     for p in slam.splats.params:
         assert torch.isfinite(p).all()
     # Adam state follows the parameters through insertion and pruning

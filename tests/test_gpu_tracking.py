@@ -127,8 +127,18 @@ def test_graphs_are_captured_once_per_map_and_reused_across_frames(cuda):
     # not bitwise: the gradient's atomics reorder between replays and the line search amplifies it
     assert torch.allclose(a.viewmat, c.viewmat, atol=5e-3) and abs(a.loss - c.loss) < 0.1 * a.loss
     assert torch.isfinite(b.viewmat).all()
-    tr.set_map(splats)
-    assert not tr._graphs
+    # a sync with a map that fits the capacity keeps the graphs; dead rows render nothing
+    assert tr.capacity >= 8_000 and tr.n_live == 8_000
+    tr.set_map(splats.mask(torch.arange(8_000, device=cuda) < 7_000))
+    assert tr.n_live == 7_000 and all(tr._graphs[k] is g for k, g in graphs.items())
+    d = tr.track_lbfgs(gt, torch.eye(4, device=cuda))
+    assert torch.isfinite(d.viewmat).all() and d.loss < 10 * a.loss
+    out = tr.splats.render([cam], [true])
+    assert int((out.radii[0, 7_000:] != 0).sum()) == 0
+    # outgrowing the capacity allocates anew and drops them
+    big, _, _, _ = _problem(cuda, n=tr.capacity + 1)
+    tr.set_map(big)
+    assert not tr._graphs and tr.capacity > 8_000 * 1.25
 
 
 def test_frozen_exposure_stays_zero(cuda):

@@ -4,7 +4,7 @@ import pytest
 import torch
 
 from gslam_b200.synthetic import smooth_trajectory
-from gslam_b200.tracking import StopOnPlateau, Tracker, _SplitTheta, constant_motion
+from gslam_b200.tracking import StopOnPlateau, Tracker, _SplitTheta, constant_motion, rigid_inverse
 from gslam_b200.primitives import Camera
 
 
@@ -53,3 +53,9 @@ def test_trajectory_is_rigid_and_starts_at_identity():
 def test_tracker_refuses_a_cpu_device():
     with pytest.raises(RuntimeError, match="CUDA"):
         Tracker(Camera(torch.eye(3), 8, 8), device="cpu")
+
+
+def test_rigid_inverse_matches_the_general_inverse():
+    T = smooth_trajectory(40)[1:]
+    assert torch.allclose(rigid_inverse(T), torch.linalg.inv(T), atol=1e-6)
+    assert torch.allclose(rigid_inverse(T[3]) @ T[3], torch.eye(4), atol=1e-6)
