@@ -64,8 +64,19 @@ __device__ __forceinline__ TileRange tile_range(const int32_t* offsets, int lin,
                                                 int64_t n_isects) {
     TileRange r;
     r.start = offsets[lin];
-    // n_isects < 0: offsets has C*T+1 entries (device-side count, gsb_tile_scan)
-    r.end = (lin == n_lin - 1 && n_isects >= 0) ? (int)n_isects : offsets[lin + 1];
+    if (n_isects >= 0) {
+        r.end = (lin == n_lin - 1) ? (int)n_isects : offsets[lin + 1];
+    } else {
+        // offsets has C*T+1 entries (device-side count, gsb_tile_scan); -n_isects - 1 is the
+        // capacity of flatten_ids (0: unbounded).  A step whose count exceeds the capacity it was
+        // captured with (the overflow flag of gsb_isect_scatter) must not read past the buffer.
+        r.end = offsets[lin + 1];
+        const int cap = (int)(-n_isects - 1);
+        if (cap > 0) {
+            r.start = min(r.start, cap);
+            r.end = min(r.end, cap);
+        }
+    }
     return r;
 }
 

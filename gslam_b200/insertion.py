@@ -28,7 +28,7 @@ import torch
 from torch import Tensor
 
 from .mapping import FlatSplats
-from .primitives import rigid_inverse
+from .primitives import affine_inverse
 from .rasterization import RasterizationOutput, get_new_splat_depth
 from .surgery import add_new_splats
 
@@ -106,7 +106,7 @@ class InsertFromDepthMap:
         pick = torch.cat(picks)
         n = pick.shape[0]
         cam_pts = backproject(intrinsics, depths)[pick]
-        c2w = rigid_inverse(viewmat)          # = torch.linalg.inv for a view matrix, without the LU + sync
+        c2w = affine_inverse(viewmat)          # = torch.linalg.inv for a view matrix, without the LU + sync
         means = cam_pts @ c2w[:3, :3].t() + c2w[:3, 3]
         colors = img.reshape(-1, 3)[pick].clamp(1e-4, 1 - 1e-4)      # logit of exact 0 / 1 is infinite
         if median_scale is None:

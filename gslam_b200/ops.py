@@ -148,7 +148,7 @@ class _Composite(torch.autograd.Function):
         C, N = rec.shape[0], rec.shape[1]
         dev = rec.device
         # offsets with C*T+1 entries carry the intersection count on the device (bin_tiles)
-        n_isects = -1 if offsets.numel() == C * tile_w * tile_h + 1 else flatten_ids.numel()
+        n_isects = -(flatten_ids.numel() + 1) if offsets.numel() == C * tile_w * tile_h + 1 else flatten_ids.numel()
         backgrounds = _c(backgrounds)
         render = torch.empty(C, height, width, CH, dtype=torch.float32, device=dev)
         alphas = torch.empty(C, height, width, 1, dtype=torch.float32, device=dev)

@@ -84,14 +84,21 @@ def pose_batch(poses: List[PoseZhou]) -> Tensor:
                       torch.stack([p.dt for p in poses]))
 
 
-def rigid_inverse(T: Tensor) -> Tensor:
-    """Inverse of a rigid [4,4] (or [...,4,4]) transform, [R^T | -R^T t]: what `torch.linalg.inv`
-    returns for the view matrices of this path (rotation from Gram-Schmidt, gslam/primitives.py:
-    15-36) without the LU factorisation, its pivoting sync and the ~170 ms solver start-up."""
-    Rt = T[..., :3, :3].transpose(-1, -2)
+def affine_inverse(T: Tensor) -> Tensor:
+    """Inverse of [A t; 0 0 0 1] (shape [...,4,4]) in closed form, [A^-1 | -A^-1 t] with A^-1 from the
+    adjugate: what the reference gets from `torch.linalg.inv` on its view matrices
+    (gslam/frontend.py:183, gslam/backend.py:764, gslam/insertion.py:218) without the LU
+    factorisation, its pivoting sync and the ~170 ms solver start-up.  Deliberately NOT the
+    transpose shortcut of a rigid matrix: the constant-motion recurrence b a^-1 b amplifies the
+    rounding-level non-orthonormality of its inputs exponentially when a^T stands in for a^-1."""
+    A = T[..., :3, :3]
+    r0, r1, r2 = A[..., 0, :], A[..., 1, :], A[..., 2, :]
+    c0, c1, c2 = torch.linalg.cross(r1, r2), torch.linalg.cross(r2, r0), torch.linalg.cross(r0, r1)
+    det = (r0 * c0).sum(-1, keepdim=True)
+    Ainv = torch.stack([c0, c1, c2], dim=-1) / det.unsqueeze(-1)
     out = torch.zeros_like(T)
-    out[..., :3, :3] = Rt
-    out[..., :3, 3] = -(Rt @ T[..., :3, 3:4])[..., 0]
+    out[..., :3, :3] = Ainv
+    out[..., :3, 3] = -(Ainv @ T[..., :3, 3:4])[..., 0]
     out[..., 3, 3] = 1.0
     return out
 

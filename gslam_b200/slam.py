@@ -43,7 +43,7 @@ from .optim import FusedAdam
 from .primitives import Camera, PoseZhou, pose_batch
 from .pruning import prune_round
 from .rasterization import RasterizationOutput, rasterization
-from .tracking import StopOnPlateau, Tracker, TrackingConfig, constant_motion, rigid_inverse
+from .tracking import StopOnPlateau, Tracker, TrackingConfig, constant_motion, affine_inverse
 
 
 @dataclass
@@ -188,7 +188,7 @@ class Slam:
         rendered depth, then the angle between the optical axes."""
         prev = self.keyframes[max(self.keyframes)].pose()
         out = self.render(torch.stack([viewmat, prev]))
-        diff = rigid_inverse(viewmat) @ prev
+        diff = affine_inverse(viewmat) @ prev
         translation = diff[:3, 3].norm()
         seen = out.depthmaps[out.alphas[..., 0] > 0.1]
         median_depth = seen.median() if seen.numel() else torch.ones((), device=self.dev)

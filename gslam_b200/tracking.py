@@ -43,7 +43,7 @@ from .graph import GraphedStep
 from .lbfgs import lbfgs_minimize
 from .losses import tracking_loss
 from .map import GaussianSplattingData
-from .primitives import Camera, pose_chain, rigid_inverse  # noqa: F401  (re-exported)
+from .primitives import Camera, pose_chain, affine_inverse  # noqa: F401  (re-exported)
 
 N_POSE = 9          # dR[6] | dt[3]
 N_THETA = 11        # ... | exposure (a, b)
@@ -385,4 +385,4 @@ def constant_motion(prev2: Optional[Tensor], prev1: Tensor) -> Tensor:
     """Initial pose of a new frame (gslam/frontend.py:176-183): pose_b @ inv(pose_a) @ pose_b."""
     if prev2 is None:
         return prev1.clone()
-    return prev1 @ rigid_inverse(prev2) @ prev1
+    return prev1 @ affine_inverse(prev2) @ prev1

@@ -144,7 +144,10 @@ int gsb_isect_offsets(const int64_t* isect_ids, int64_t n_isects, int C, int til
 
 /* K6: per-tile front-to-back compositing (reference gslam/rasterization.py:325-339).
  * offsets holds C*T entries and n_isects closes the last tile; pass n_isects < 0 when
- * offsets has C*T+1 entries (gsb_tile_scan), so that no host-side count is needed.
+ * offsets has C*T+1 entries (gsb_tile_scan), so that no host-side count is needed:
+ * -n_isects - 1 is then the number of entries flatten_ids can hold (0 = trust offsets), and
+ * tile ranges are clipped to it, so a step with more intersections than the buffers were
+ * sized for (overflow flag of gsb_isect_scatter) stays in bounds.
  * backgrounds[C,5] may be NULL.  n_touched[C,N] i64 (the reference's dtype,
  * gslam/rasterization.py:352) must be zeroed by the caller
  * (NULL skips the count).  Outputs render[C,H,W,5], alphas[C,H,W], last_ids[C,H,W].

@@ -115,6 +115,36 @@ def test_bin_tiles_long_segments_and_capacity(cuda):
         ops.isect_capacity = None
 
 
+def test_overflowed_capacity_step_stays_in_bounds(cuda):
+    """A step with more intersections than its (graph-captured) key buffers hold raises the overflow
+    flag and renders a truncated image, but forward and backward never read past the buffers."""
+    sc = make_scene(30000, 2, "tum", 0.5).to(cuda)
+    ps = [p.clone().requires_grad_(True) for p in sc.params()]
+    vm = sc.viewmats.clone().requires_grad_(True)
+    bg = torch.zeros(2, 3, device=cuda)
+
+    def run():
+        out = rasterization(ps[0], ps[1], ps[2], ps[3], ps[4], vm, sc.Ks, sc.width, sc.height, packed=False,
+                            backgrounds=bg, render_mode="RGB+D", log_uncertainties=ps[5])
+        (out.render.sum() + out.alphas.sum()).backward()
+        return out
+    full = run()
+    I = int(ops.last_n_isects.item())
+    try:
+        for cap in (I // 3, 64, I - 1):
+            ops.isect_capacity = cap
+            out = run()
+            torch.cuda.synchronize()
+            assert int(ops.last_overflow.item()) == 1 and out.flatten_ids.numel() == cap
+            assert torch.isfinite(out.render).all() and torch.isfinite(vm.grad).all()
+        ops.isect_capacity = I + 7
+        out = run()
+        assert int(ops.last_overflow.item()) == 0
+        assert torch.allclose(out.render, full.render, atol=1e-6)
+    finally:
+        ops.isect_capacity = None
+
+
 def test_sort_random_keys_stable(cuda):
     g = torch.Generator().manual_seed(3)
     for n, bits in [(1, 40), (1000, 44), (100_000, 49), (300_001, 33)]:

@@ -4,7 +4,7 @@ import pytest
 import torch
 
 from gslam_b200.synthetic import smooth_trajectory
-from gslam_b200.tracking import StopOnPlateau, Tracker, _SplitTheta, constant_motion, rigid_inverse
+from gslam_b200.tracking import StopOnPlateau, Tracker, _SplitTheta, constant_motion, affine_inverse
 from gslam_b200.primitives import Camera
 
 
@@ -55,7 +55,20 @@ def test_tracker_refuses_a_cpu_device():
         Tracker(Camera(torch.eye(3), 8, 8), device="cpu")
 
 
-def test_rigid_inverse_matches_the_general_inverse():
+def test_affine_inverse_matches_the_general_inverse():
     T = smooth_trajectory(40)[1:]
-    assert torch.allclose(rigid_inverse(T), torch.linalg.inv(T), atol=1e-6)
-    assert torch.allclose(rigid_inverse(T[3]) @ T[3], torch.eye(4), atol=1e-6)
+    assert torch.allclose(affine_inverse(T), torch.linalg.inv(T), atol=1e-6)
+    assert torch.allclose(affine_inverse(T[3]) @ T[3], torch.eye(4), atol=1e-6)
+    skew = T[5].clone()
+    skew[:3, :3] = skew[:3, :3] * torch.tensor([1.1, 0.9, 1.3]) + 0.05       # not a rotation
+    assert torch.allclose(affine_inverse(skew), torch.linalg.inv(skew), atol=1e-5)
+
+
+def test_constant_motion_recurrence_stays_orthonormal():
+    # 300 chained extrapolations: the non-orthonormality must grow slowly (linearly), not explode
+    step = smooth_trajectory(3)[1]
+    a, b = torch.eye(4), step.clone()
+    for _ in range(300):
+        a, b = b, constant_motion(a, b)
+    R = b[:3, :3]
+    assert (R @ R.t() - torch.eye(3)).abs().max() < 5e-3       # torch.linalg.inv drifts alike (1e-3)
