@@ -157,7 +157,7 @@ class MappingStep:
 
     def __call__(self, viewmats: Tensor, Ks: Tensor, gt_imgs: Tensor, exposure: Optional[Tensor],
                  width: int, height: int, n_views_total: int, background: Optional[Tensor] = None,
-                 step_optimizer: bool = True) -> MappingStepResult:
+                 step_optimizer: bool = True, gt_depths: Optional[Tensor] = None) -> MappingStepResult:
         P = self.splats.params
         for p in P:
             p.grad = None
@@ -172,6 +172,12 @@ class MappingStep:
         if self.tv_w:
             # a sum (not a mean) over this rank's views: no share factor (gslam/backend.py:297-318)
             loss = loss + self.tv_w * edge_aware_tv(out.depthmaps, out.rgbs, out.alphas[..., 0] > 0.4)
+        if gt_depths is not None:
+            # use_gt_depths (gslam/backend.py:320-323): 0.1 * mean |depth - gt| over gt > 0, a mean over
+            # the window's valid pixels: this rank's share is its valid-pixel fraction of the window total
+            valid = (gt_depths > 0).to(out.depthmaps.dtype)
+            n_valid = allreduce_sum_(valid.sum().view(1).clone(), self.group).clamp_min(1.0)
+            loss = loss + 0.1 * ((out.depthmaps - gt_depths).abs() * valid).sum() / n_valid[0]
         from . import ops
         n = self.splats.n
         ops.grad_tail_floats = n + 2          # room behind the flat gradient for counts and loss scalars

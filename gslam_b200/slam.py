@@ -70,6 +70,7 @@ class MapConfig:
     densify_every: int = 200                # `(self.total_step % 200) == 0` (:328)
     grow_grad2d: float = 0.0002             # InsertUsingImagePlaneGradients(0.0002, 0.01) (:147-150)
     grow_scale3d: float = 0.01
+    use_gt_depths: bool = False             # RGB-D mode (:111): depth terms in mapping and tracking
     optimize_poses: bool = True             # optimize_poses_lbfgs after every idle mapping round (:851)
 
 
@@ -80,6 +81,7 @@ class Keyframe:
     pose: PoseZhou
     exposure: Tensor            # [2], fixed once the frame is a keyframe (:660-662)
     est_depths: Optional[Tensor] = None
+    gt_depth: Optional[Tensor] = None
 
 
 @dataclass
@@ -111,6 +113,8 @@ class Slam:
         if self.dev.type != "cuda":
             raise RuntimeError("gslam_b200.slam.Slam needs a CUDA device (no CPU fallback)")
         self.gen = torch.Generator(device=self.dev).manual_seed(seed)
+        track_conf = track_conf or TrackingConfig()
+        track_conf.use_gt_depths = self.conf.use_gt_depths
         self.tracker = Tracker(self.camera, track_conf, device)
         c = self.conf
         self.insertion = InsertFromDepthMap(0.1 * c.initial_scale, 0.2 * c.initial_scale, 0.1,
@@ -149,7 +153,7 @@ class Slam:
                     for kf in self.keyframes.values() if kf.est_depths is not None]
 
     # ---- backend ---------------------------------------------------------------------------------
-    def initialize(self, img: Tensor) -> None:
+    def initialize(self, img: Tensor, gt_depth: Optional[Tensor] = None) -> None:
         """Backend.initialize (gslam/backend.py:604-631)."""
         H, W = self.camera.height, self.camera.width
         d = self.dev
@@ -159,14 +163,16 @@ class Slam:
         mock_alphas = torch.full((1, H, W, 1), 0.01, device=d)
         mock = RasterizationOutput(None, mock_alphas, mock_depth)
         pose = PoseZhou(torch.eye(4, device=d)).to(d)
-        kf = Keyframe(0, img, pose, torch.zeros(2, device=d))
+        kf = Keyframe(0, img, pose, torch.zeros(2, device=d), gt_depth=gt_depth)
         self.keyframes[0] = kf
         self.stats.inserted += self.insertion.step(self.splats, self.opt, mock, self.camera.intrinsics,
                                                    torch.eye(4, device=d), img, self.conf.n_init_splats,
+                                                   gt_depthmap=gt_depth if self.conf.use_gt_depths else None,
                                                    generator=self.gen)
         self.stats.keyframes = 1
 
-    def add_keyframe(self, index: int, img: Tensor, viewmat: Tensor, exposure: Tensor) -> None:
+    def add_keyframe(self, index: int, img: Tensor, viewmat: Tensor, exposure: Tensor,
+                     gt_depth: Optional[Tensor] = None) -> None:
         """Backend.add_keyframe (gslam/backend.py:633-679)."""
         out = self.render(viewmat.view(1, 4, 4))
         out.depthmaps = out.depthmaps * self.conf.initial_scale
@@ -174,7 +180,8 @@ class Slam:
                                                    img, self.conf.n_keyframe_splats, keyframes=self._views(),
                                                    generator=self.gen)
         pose = PoseZhou(viewmat.detach().clone()).to(self.dev)
-        self.keyframes[index] = Keyframe(index, img, pose, exposure.detach().clone(), out.depthmaps[0].clone())
+        self.keyframes[index] = Keyframe(index, img, pose, exposure.detach().clone(), out.depthmaps[0].clone(),
+                                         gt_depth)
         group = {"params": [pose.dR, pose.dt], "lr": self.conf.pose_optim_lr}
         if self.pose_opt is None:
             self.pose_opt = FusedAdam([group])
@@ -214,6 +221,7 @@ class Slam:
         exposure = torch.stack([k.exposure for k in window])
         Ks = self.camera.intrinsics.expand(len(window), 3, 3).contiguous()
         poses = [k.pose for k in window]
+        gt_depths = torch.stack([k.gt_depth for k in window]) if c.use_gt_depths else None
         for _ in range(n_iters):
             self.total_step += 1
             for p in poses:
@@ -221,7 +229,8 @@ class Slam:
                 p.dt.grad = None
             densify = c.densify_every > 0 and self.total_step % c.densify_every == 0
             self.step.retain_means2d_grad = densify
-            res = self.step(pose_batch(poses), Ks, gt, exposure, W, H, len(window), step_optimizer=not densify)
+            res = self.step(pose_batch(poses), Ks, gt, exposure, W, H, len(window), step_optimizer=not densify,
+                            gt_depths=gt_depths)
             if densify:
                 # the reference densifies between backward and the optimizer step (:328-351): the
                 # parameters it re-creates carry no gradient, so that iteration takes no splat step and
@@ -329,14 +338,14 @@ class Slam:
         self.tracker.set_map(GaussianSplattingData(P[0], P[1], P[2], P[3], P[4], P[5], ages))
 
     # ---- one frame --------------------------------------------------------------------------------
-    def process_frame(self, img: Tensor, idle_rounds: int = 1) -> Tensor:
+    def process_frame(self, img: Tensor, idle_rounds: int = 1, gt_depth: Optional[Tensor] = None) -> Tensor:
         """Track `img` [H,W,3] (device, values in [0,1]) and let the backend work; returns the frame's
         world->camera matrix."""
         idx = self.stats.frames
         sync = torch.cuda.synchronize
         if idx == 0:
             t0 = time.perf_counter()
-            self.initialize(img)
+            self.initialize(img, gt_depth)
             self.pause_map_optim = False
             self.optimize_map(self.conf.num_iters_initialization, prune=False, regularize=True)
             self.sync()
@@ -348,7 +357,8 @@ class Slam:
             t0 = time.perf_counter()
             prev2 = self.frame_poses[-2] if len(self.frame_poses) > 1 else None
             init = constant_motion(prev2, self.frame_poses[-1])
-            r = self.tracker.track_lbfgs(img, init, self.last_exposure)
+            r = self.tracker.track_lbfgs(img, init, self.last_exposure,
+                                         gt_depth if self.conf.use_gt_depths else None)
             viewmat, self.last_exposure = r.viewmat, r.exposure
             self.stats.tracking_evals += r.n_evals
             self.stats.tracking_syncs += r.n_syncs
@@ -358,7 +368,7 @@ class Slam:
             self.stats.t_tracking += t1 - t0
             if self.to_insert_keyframe(viewmat):
                 self.pause_map_optim = False
-                self.add_keyframe(idx, img, viewmat, r.exposure)
+                self.add_keyframe(idx, img, viewmat, r.exposure, gt_depth)
                 self.optimize_map(1, prune=True, regularize=False)
             for _ in range(idle_rounds):                  # Backend.run with an empty queue (:846-852)
                 if self.pause_map_optim:
@@ -380,13 +390,13 @@ class Slam:
 
 @torch.no_grad()
 def synthetic_sequence(n_frames: int, n_gauss: int = 20000, scale: float = 1.0, device="cuda", seed: int = 0):
-    """(camera, images [F,H,W,3], gt viewmats [F,4,4]): renders of a random `synthetic.make_scene` map
+    """(camera, images [F,H,W,3], gt viewmats [F,4,4], depths [F,H,W]): renders of a random `synthetic.make_scene` map
     along `synthetic.smooth_trajectory`, produced by this package's own rasterizer (the data of cfg5)."""
     from .synthetic import make_scene, smooth_trajectory
     sc = make_scene(n_gauss, 1, "tum", scale, seed=seed).to(device)
     cam = Camera(sc.Ks[0].clone(), sc.height, sc.width)
     poses = smooth_trajectory(n_frames).to(device)
-    imgs = []
+    imgs, depths = [], []
     P = sc.params()
     for i in range(0, n_frames, 8):
         vm = poses[i:i + 8].contiguous()
@@ -395,19 +405,20 @@ def synthetic_sequence(n_frames: int, n_gauss: int = 20000, scale: float = 1.0, 
                             sc.height, packed=False, render_mode="RGB+D", log_uncertainties=P[5],
                             backgrounds=torch.full((C, 3), 0.5, device=device))
         imgs.append(out.rgbs.clamp(0, 1).clone())
-    return cam, torch.cat(imgs), poses
+        depths.append(out.depthmaps.clone())          # accumulated (alpha-unnormalised) depth, like the map's
+    return cam, torch.cat(imgs), poses, torch.cat(depths)
 
 
 def run_sequence(n_frames: int, n_gauss: int = 20000, scale: float = 1.0, device="cuda", seed: int = 0,
                  map_conf: Optional[MapConfig] = None, track_conf: Optional[TrackingConfig] = None,
                  idle_rounds: int = 1):
     """cfg5: the whole loop over a synthetic sequence -> (Slam, frames/s, gt viewmats)."""
-    cam, imgs, gt_poses = synthetic_sequence(n_frames, n_gauss, scale, device, seed)
+    cam, imgs, gt_poses, depths = synthetic_sequence(n_frames, n_gauss, scale, device, seed)
     slam = Slam(cam, map_conf, track_conf, device, seed)
     torch.cuda.synchronize()
     t0 = time.perf_counter()
     for i in range(n_frames):
-        slam.process_frame(imgs[i], idle_rounds)
+        slam.process_frame(imgs[i], idle_rounds, depths[i])
     torch.cuda.synchronize()
     dt = time.perf_counter() - t0
     return slam, n_frames / dt, gt_poses

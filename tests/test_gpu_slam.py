@@ -38,7 +38,7 @@ def test_short_sequence_runs_every_stage(cuda):
 
 def test_window_pose_lbfgs_moves_only_the_free_keyframes(cuda):
     from gslam_b200.slam import Slam, synthetic_sequence
-    cam, imgs, gt_poses = synthetic_sequence(12, 6_000, 0.5, cuda)
+    cam, imgs, gt_poses, _ = synthetic_sequence(12, 6_000, 0.5, cuda)
     slam = Slam(cam, MapConfig(num_iters_initialization=60), TrackingConfig(lbfgs_max_iter=4), cuda)
     slam.process_frame(imgs[0])
     # a second keyframe whose pose starts a little off the tracked one
@@ -55,3 +55,17 @@ def test_window_pose_lbfgs_moves_only_the_free_keyframes(cuda):
     n0 = slam.splats.n
     slam.run_pruning()
     assert slam.splats.n <= n0
+
+
+def test_rgbd_sequence_follows_the_ground_truth_trajectory(cuda):
+    # use_gt_depths (gslam/backend.py:111, :320-323; gslam/frontend.py:132-136): with depth supervision
+    # the gauge is fixed by frame 0 = identity, so the tracked poses are comparable with the truth
+    conf = MapConfig(num_iters_initialization=150, use_gt_depths=True)
+    slam, fps, gt_poses = run_sequence(16, n_gauss=6_000, scale=0.5, device=cuda, map_conf=conf)
+    est = torch.stack(slam.frame_poses)
+    err_t = (est[:, :3, 3] - gt_poses[:, :3, 3]).norm(dim=1)
+    moved = gt_poses[-1, :3, 3].norm()
+    assert float(err_t.max()) < 0.5 * float(moved) + 5e-3, (err_t.tolist(), float(moved))
+    rel = est[:, :3, :3] @ gt_poses[:, :3, :3].transpose(1, 2)
+    assert float((rel - torch.eye(3, device=cuda)).norm(dim=(1, 2)).max()) < 0.05
+    assert slam.tracker.gt_depth is not None

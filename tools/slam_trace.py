@@ -11,11 +11,12 @@ from gslam_b200.tracking import TrackingConfig                       # noqa: E40
 F = int(sys.argv[1]) if len(sys.argv) > 1 else 30
 scale = float(sys.argv[2]) if len(sys.argv) > 2 else 1.0
 dev = torch.device("cuda:0")
-cam, imgs, gt = synthetic_sequence(F, 20_000, scale, dev)
-slam = Slam(cam, MapConfig(), TrackingConfig(), dev)
+cam, imgs, gt, depths = synthetic_sequence(F, 20_000, scale, dev)
+rgbd = len(sys.argv) > 3 and sys.argv[3] == 'rgbd'
+slam = Slam(cam, MapConfig(use_gt_depths=rgbd), TrackingConfig(), dev)
 for i in range(F):
     kf0, it0, ev0 = slam.stats.keyframes, slam.stats.mapping_iters, slam.stats.tracking_evals
-    vm = slam.process_frame(imgs[i])
+    vm = slam.process_frame(imgs[i], 1, depths[i])
     st = slam.stats
     rel = (vm @ torch.linalg.inv(gt[i]))
     print(f"frame {i:3d} track_loss {st.last_tracking_loss:.5f} evals {st.tracking_evals - ev0:3d} "
