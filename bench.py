@@ -261,7 +261,7 @@ def tracking_closure_leg(args, dev):
         for q in (pose.dR, pose.dt, exposure):
             q.grad = None
         out = splats([cam], [pose], render_depth=True)
-        loss = tracking_loss(out.render, gt, exposure, "active-nerf")
+        loss = tracking_loss(out.render, gt, exposure, "active-nerf", unit_upstream=True)
         loss.backward()
         opt.step()
         return loss
@@ -389,7 +389,7 @@ def run_ours(args):
 
     def loss_fn(out, gt_):
         # active-NeRF photometric term of the tracking step (gslam/frontend.py:113-129), fused kernel
-        return tracking_loss(out.render, gt_, None, "active-nerf")
+        return tracking_loss(out.render, gt_, None, "active-nerf", unit_upstream=True)   # backward() starts here
 
     def step(ps, vm_, K_, gt_):
         for p in ps:

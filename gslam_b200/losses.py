@@ -73,7 +73,7 @@ def fused_ssim(img1: Tensor, img2: Tensor, padding: str = "same", train: bool = 
 
 class _PhotometricSSIM(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, render, gt, exposure, ssim_weight, mode):
+    def forward(ctx, render, gt, exposure, ssim_weight, mode, unit_upstream=False):
         ctx.set_materialize_grads(False)
         # render [C,H,W,5] = (r, g, b, depth, beta); gt [C,H,W,3]; exposure [C,2] or None
         assert render.is_cuda and render.is_contiguous() and render.shape[-1] == 5
@@ -103,6 +103,7 @@ class _PhotometricSSIM(torch.autograd.Function):
             total = torch.sub(total, ssim_sum[0], alpha=ssim_weight / ctx.count) + ssim_weight
         ctx.save_for_backward(render, gt, maps, v_render, v_exp)
         ctx.ssim_weight = ssim_weight
+        ctx.unit_upstream = bool(unit_upstream) and ssim_weight == 0.0
         ctx.mark_non_differentiable(photo)
         return total, photo
 
@@ -111,6 +112,9 @@ class _PhotometricSSIM(torch.autograd.Function):
         render, gt, maps, v_render, v_exp = ctx.saved_tensors
         C, H, W, _ = render.shape
         g = g.contiguous()
+        if ctx.unit_upstream:
+            # the caller calls backward() on this loss itself: the incoming gradient is exactly 1
+            return v_render, None, v_exp, None, None, None
         call("gsb_scale_by_scalar", ptr(v_render), v_render.numel(), ptr(g), stream())
         if maps is not None:
             img1 = render[..., :3].permute(0, 3, 1, 2)
@@ -119,7 +123,7 @@ class _PhotometricSSIM(torch.autograd.Function):
             call("gsb_ssim_bwd", ptr(img1), ptr(img2), _strides(img1), _strides(img2), C, 3, H, W,
                  ptr(maps[0]), ptr(maps[1]), ptr(maps[2]), ptr(g), -ctx.ssim_weight / ctx.count, ptr(v1),
                  _strides(v1), 1, stream())
-        return v_render, None, (v_exp * g if v_exp is not None else None), None, None
+        return v_render, None, (v_exp * g if v_exp is not None else None), None, None, None
 
 
 def photometric_ssim_loss(render: Tensor, gt: Tensor, exposure: Optional[Tensor] = None,
@@ -132,9 +136,14 @@ def photometric_ssim_loss(render: Tensor, gt: Tensor, exposure: Optional[Tensor]
 
 
 def tracking_loss(render: Tensor, gt: Tensor, exposure: Optional[Tensor] = None,
-                  kind: str = "active-nerf") -> Tensor:
-    """gslam/frontend.py:113-129 on the [1,H,W,5] render, exposure = (a, b) as [2] or [1,2]."""
+                  kind: str = "active-nerf", unit_upstream: bool = False) -> Tensor:
+    """gslam/frontend.py:113-129 on the [1,H,W,5] render, exposure = (a, b) as [2] or [1,2].
+
+    unit_upstream=True is the caller's promise that the loss reaches `backward()` with coefficient
+    exactly 1 (`loss.backward()`, or `(loss + other).backward()`), as every tracking loop of the
+    reference does: the backward then hands on the gradient the forward kernel already wrote instead
+    of multiplying 1.5 M floats by 1.0 in one more pass.  A scaled use of such a loss is WRONG."""
     if exposure is not None and exposure.dim() == 1:
         exposure = exposure.view(1, 2)
-    total, _ = _PhotometricSSIM.apply(render, gt, exposure, 0.0, PHOTO_MODES[kind])
+    total, _ = _PhotometricSSIM.apply(render, gt, exposure, 0.0, PHOTO_MODES[kind], unit_upstream)
     return total

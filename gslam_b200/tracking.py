@@ -196,7 +196,8 @@ class Tracker:
         viewmats = pose_chain(self.Rt, dR, dt)
         out = self.splats._rasterize([self.camera], viewmats, "RGB+D", 0.5)     # = splats.render(...), gslam/map.py:50-76
         exposure = ex if self.conf.learn_exposure_params else None
-        loss = tracking_loss(out.render, self.gt, exposure, self.conf.photometric_loss)
+        # backward() below starts from this loss (plus, at most, an added depth term): coefficient 1
+        loss = tracking_loss(out.render, self.gt, exposure, self.conf.photometric_loss, unit_upstream=True)
         if self.conf.use_gt_depths:
             # (rendered - gt)[gt > 0].abs().mean() * 0.01 without the data-dependent shape
             valid = (self.gt_depth > 0).float()

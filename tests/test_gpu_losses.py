@@ -84,7 +84,8 @@ def test_photometric_ssim_loss_matches_mapping_loss(cuda):
 
 
 @pytest.mark.parametrize("kind", ["active-nerf", "l1", "mse"])
-def test_tracking_loss_modes(cuda, kind):
+@pytest.mark.parametrize("unit", [False, True])
+def test_tracking_loss_modes(cuda, kind, unit):
     render, gt, exposure = _render(1, 32, 48, seed=3)
     exposure = exposure[0]
     rr = render.clone().requires_grad_(True)
@@ -100,7 +101,8 @@ def test_tracking_loss_modes(cuda, kind):
     ref.backward()
     rg = render.to(cuda).requires_grad_(True)
     eg = exposure.to(cuda).requires_grad_(True)
-    out = tracking_loss(rg, gt.to(cuda), eg, kind=kind)
+    # unit=True: the caller promises backward() starts at this loss, so the x1.0 pass is skipped
+    out = tracking_loss(rg, gt.to(cuda), eg, kind=kind, unit_upstream=unit)
     out.backward()
     assert abs(out.item() - ref.item()) < 1e-5 * max(1.0, abs(ref.item()))
     assert rel_err(rg.grad, rr.grad) < 1e-3
