@@ -122,7 +122,12 @@ def edge_aware_tv(depth: Tensor, rgb: Tensor, mask: Tensor) -> Tensor:
     return (ddx * wx * mask[..., :, :-1]).sum() + (ddy * wy * mask[..., :-1, :]).sum()
 
 
+LOCAL = "local"      # MappingStep(group=LOCAL): this rank maps on its own even inside a multi-rank job
+
+
 def allreduce_sum_(t: Tensor, group=None) -> Tensor:
+    if isinstance(group, str) and group == LOCAL:
+        return t
     if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
         dist.all_reduce(t, op=dist.ReduceOp.SUM, group=group)
     return t

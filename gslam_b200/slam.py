@@ -38,7 +38,7 @@ from .lbfgs import lbfgs_minimize
 from .losses import photometric_ssim_loss
 from .insertion import InsertFromDepthMap, InsertUsingImagePlaneGradients, KeyframeView
 from .map import GaussianSplattingData
-from .mapping import DEFAULT_LRS, PARAM_NAMES, FlatSplats, MappingStep
+from .mapping import DEFAULT_LRS, LOCAL, PARAM_NAMES, FlatSplats, MappingStep
 from .optim import FusedAdam
 from .primitives import Camera, PoseZhou, pose_batch
 from .pruning import prune_round
@@ -134,7 +134,8 @@ class Slam:
         self.pose_opt: Optional[FusedAdam] = None
         self.step = MappingStep(self.splats, self.opt, ssim_weight=c.ssim_weight,
                                 isotropic_weight=c.isotropic_regularization_weight,
-                                opacity_decay=c.opacity_decay)
+                                opacity_decay=c.opacity_decay,
+                                group=LOCAL)       # one process tracks and maps: no collective, whatever the job size
         self.bg1 = torch.zeros(1, 3, device=self.dev)
 
     # ---- rendering helpers ----------------------------------------------------------------------

@@ -119,3 +119,42 @@ def test_edge_aware_tv_matches_oracle():
     depth, rgb = torch.rand(2, 12, 17, generator=g), torch.rand(2, 12, 17, 3, generator=g)
     mask = torch.rand(2, 12, 17, generator=g) > 0.4
     torch.testing.assert_close(edge_aware_tv(depth, rgb, mask), R.edge_aware_tv(depth, rgb, mask))
+
+
+def _run_local(rank, world, port, q):
+    """Rank 0 runs a whole LOCAL mapping step while rank 1 goes straight to the barrier (what bench.py's
+    sequence leg does under torchrun): no collective may be issued by the step."""
+    from gslam_b200.mapping import LOCAL
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    torch.set_num_threads(2)
+    val = None
+    if rank == 0:
+        sc = make_scene(N_GAUSS, N_VIEWS, "tum", 0.1)
+        gt = target_images(N_VIEWS, sc.height, sc.width)
+        splats = FlatSplats(sc.params())
+        step = MappingStep(splats, _Adam(splats.params), render_fn=_oracle_render, loss_fn=_oracle_loss,
+                           depth_tv_weight=1e-6, group=LOCAL)
+        res = step(sc.viewmats, sc.Ks, gt, torch.zeros(N_VIEWS, 2), sc.width, sc.height, N_VIEWS)
+        val = float(res.total)
+    q.put((rank, val))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.timeout(600)
+def test_local_group_issues_no_collective_inside_a_two_rank_job():
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    procs = [ctx.Process(target=_run_local, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    out = dict(q.get(timeout=300) for _ in range(2))
+    for p in procs:
+        p.join(timeout=120)
+        assert p.exitcode == 0
+    one = _launch(1)[0]
+    assert out[1] is None and abs(out[0] - one[3]) < 1e-4 * max(1.0, abs(one[3]))
