@@ -115,8 +115,12 @@ isect_scatter_kernel(const float* __restrict__ means2d, const int32_t* __restric
 // ranks its keys inside the reserved ranges with shared-memory atomics.  The per-key returning
 // global atomic of the kernel above (whose round trip bounds it) is gone; the order inside a
 // segment is arbitrary either way, the segment sort fixes it.
-#define SCL_THREADS 1024
-template <int GPT>
+//
+// The chunk a CTA takes is sized to the launch (gsb_isect_scatter): 2048 Gaussians at map sizes where
+// that still gives a grid of 64+ CTAs, 256 or 64 for the small maps of a starting sequence (a few
+// thousand splats that each cover hundreds of tiles), where three 2048-chunks would leave the
+// million shared-memory atomics of the expansion to three SMs.
+template <int SCL_THREADS, int GPT>
 __global__ void __launch_bounds__(SCL_THREADS)
 isect_scatter_local_kernel(const float* __restrict__ means2d, const int32_t* __restrict__ radii,
                            const float* __restrict__ rec, int N, int tile_w, int tile_h,
@@ -171,6 +175,23 @@ isect_scatter_local_kernel(const float* __restrict__ means2d, const int32_t* __r
     }
 }
 
+template <int THREADS, int GPT>
+static int launch_scatter_local(const float* means2d, const int32_t* radii, const float* rec, int C, int N,
+                                int tile_w, int tile_h, int32_t* cursors, int64_t capacity, uint64_t* dk,
+                                int32_t* overflow, size_t smem, void* stream) {
+    static bool attr_set = false;
+    if (!attr_set) {
+        GSB_CUDA(cudaFuncSetAttribute(isect_scatter_local_kernel<THREADS, GPT>,
+                                      cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+        attr_set = true;
+    }
+    dim3 grid((N + THREADS * GPT - 1) / (THREADS * GPT), C);
+    isect_scatter_local_kernel<THREADS, GPT><<<grid, THREADS, smem, gsb_stream(stream)>>>(
+        means2d, radii, rec, N, tile_w, tile_h, cursors, capacity, dk, overflow);
+    GSB_LAUNCH_CHECK();
+    return 0;
+}
+
 GSB_API int gsb_isect_scatter(const float* means2d, const int32_t* radii, const float* rec, int C, int N,
                               int tile_w, int tile_h, int32_t* cursors, int64_t capacity,
                               int64_t* depth_id, int32_t* overflow, void* stream) {
@@ -182,20 +203,18 @@ GSB_API int gsb_isect_scatter(const float* means2d, const int32_t* radii, const 
     const size_t smem = (size_t)tile_w * tile_h * 2 * sizeof(int32_t);
     if (smem <= 96 * 1024 && C <= 65535) {
         // chunk = 2048 Gaussians of one camera: ~10 keys per (CTA, tile) at SLAM densities
-        // (measured: 1024 the same, 4096 slower -- too few CTAs)
-        constexpr int GPT = 2;
-        static bool attr_set = false;
-        if (!attr_set) {
-            GSB_CUDA(cudaFuncSetAttribute(isect_scatter_local_kernel<GPT>,
-                                          cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
-            attr_set = true;
-        }
-        dim3 grid((N + SCL_THREADS * GPT - 1) / (SCL_THREADS * GPT), C);
-        isect_scatter_local_kernel<GPT><<<grid, SCL_THREADS, smem, gsb_stream(stream)>>>(
-            means2d, radii, rec, N, tile_w, tile_h, cursors, capacity,
-            reinterpret_cast<uint64_t*>(depth_id), overflow);
-        GSB_LAUNCH_CHECK();
-        return 0;
+        // (measured at 200k: 1024 the same, 4096 slower -- too few CTAs); smaller chunks only when
+        // 2048 would leave most SMs without a CTA
+        uint64_t* dk = reinterpret_cast<uint64_t*>(depth_id);
+        const int64_t want = 64;
+        if ((int64_t)C * ((N + 2047) / 2048) >= want)
+            return launch_scatter_local<1024, 2>(means2d, radii, rec, C, N, tile_w, tile_h, cursors, capacity, dk,
+                                                 overflow, smem, stream);
+        if ((int64_t)C * ((N + 255) / 256) >= want)
+            return launch_scatter_local<256, 1>(means2d, radii, rec, C, N, tile_w, tile_h, cursors, capacity, dk,
+                                                overflow, smem, stream);
+        return launch_scatter_local<64, 1>(means2d, radii, rec, C, N, tile_w, tile_h, cursors, capacity, dk,
+                                           overflow, smem, stream);
     }
     int blocks = (int)((CN + 255) / 256);
     isect_scatter_kernel<<<blocks, 256, 0, gsb_stream(stream)>>>(

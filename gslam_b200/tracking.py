@@ -150,6 +150,7 @@ class Tracker:
         self.splats: Optional[GaussianSplattingData] = None
         self.capacity = 0
         self.n_live = 0
+        self.n_captures = 0          # graph captures so far (2 per map capacity, more only after an overflow)
         self._graphs = {}
         self.headroom = 1.5          # capacity of the captured key buffers over the measured count
         self.n_evals = 0
@@ -253,6 +254,7 @@ class Tracker:
             saved = [t.clone() for t in (self.theta.detach(), self.m, self.v, self.step_no, self.lr_scale,
                                          self.ring_pos)]
             g = GraphedStep(fn, headroom=self.headroom)
+            self.n_captures += 1
             # the eager warm-up runs of the capture moved the unknowns; put them back
             with torch.no_grad():
                 for t, s in zip((self.theta, self.m, self.v, self.step_no, self.lr_scale, self.ring_pos), saved):

@@ -16,6 +16,7 @@ rgbd = len(sys.argv) > 3 and sys.argv[3] == 'rgbd'
 slam = Slam(cam, MapConfig(use_gt_depths=rgbd), TrackingConfig(), dev)
 for i in range(F):
     kf0, it0, ev0 = slam.stats.keyframes, slam.stats.mapping_iters, slam.stats.tracking_evals
+    tt0, tm0 = slam.stats.t_tracking, slam.stats.t_mapping
     vm = slam.process_frame(imgs[i], 1, depths[i])
     st = slam.stats
     rel = (vm @ torch.linalg.inv(gt[i]))
@@ -23,5 +24,6 @@ for i in range(F):
           f"kf {'+' if st.keyframes > kf0 else ' '}{st.keyframes:3d} map_iters +{st.mapping_iters - it0:3d} "
           f"photo {st.last_photometric:.4f} N {st.n_splats:5d} paused {int(slam.pause_map_optim)} "
           f"|t_est| {float(vm[:3, 3].norm()):.4f} |t_gt| {float(gt[i][:3, 3].norm()):.4f} "
-          f"rot_err {float((rel[:3, :3] - torch.eye(3, device=dev)).norm()):.4f}")
+          f"rot_err {float((rel[:3, :3] - torch.eye(3, device=dev)).norm()):.4f} "
+          f"track {1e3 * (st.t_tracking - tt0):6.1f} ms map {1e3 * (st.t_mapping - tm0):6.1f} ms captures {slam.tracker.n_captures}")
 print(st)
