@@ -117,7 +117,7 @@ isect_scatter_kernel(const float* __restrict__ means2d, const int32_t* __restric
 // segment is arbitrary either way, the segment sort fixes it.
 //
 // The chunk a CTA takes is sized to the launch (gsb_isect_scatter): 2048 Gaussians at map sizes where
-// that still gives a grid of 64+ CTAs, 256 or 64 for the small maps of a starting sequence (a few
+// that still gives a grid of 64+ CTAs, 256, 64 or 32 for the small maps of a starting sequence (a few
 // thousand splats that each cover hundreds of tiles), where three 2048-chunks would leave the
 // million shared-memory atomics of the expansion to three SMs.
 template <int SCL_THREADS, int GPT>
@@ -213,7 +213,10 @@ GSB_API int gsb_isect_scatter(const float* means2d, const int32_t* radii, const 
         if ((int64_t)C * ((N + 255) / 256) >= want)
             return launch_scatter_local<256, 1>(means2d, radii, rec, C, N, tile_w, tile_h, cursors, capacity, dk,
                                                 overflow, smem, stream);
-        return launch_scatter_local<64, 1>(means2d, radii, rec, C, N, tile_w, tile_h, cursors, capacity, dk,
+        if ((int64_t)C * ((N + 63) / 64) >= 2 * want)
+            return launch_scatter_local<64, 1>(means2d, radii, rec, C, N, tile_w, tile_h, cursors, capacity, dk,
+                                               overflow, smem, stream);
+        return launch_scatter_local<32, 1>(means2d, radii, rec, C, N, tile_w, tile_h, cursors, capacity, dk,
                                            overflow, smem, stream);
     }
     int blocks = (int)((CN + 255) / 256);

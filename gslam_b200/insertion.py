@@ -61,7 +61,8 @@ def knn_mean_distance(points: Tensor, k: int = 3, chunk: int = 4096) -> Tensor:
     kk = min(k, n - 1)
     out = []
     for i in range(0, n, chunk):
-        d = torch.cdist(points[i:i + chunk], points)
+        # exact differences, not the |a|^2 + |b|^2 - 2ab GEMM form (cancellation at small distances)
+        d = torch.cdist(points[i:i + chunk], points, compute_mode="donot_use_mm_for_euclid_dist")
         out.append(d.topk(kk + 1, dim=1, largest=False).values[:, 1:].mean(dim=1))
     return torch.cat(out)
 

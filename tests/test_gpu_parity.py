@@ -64,9 +64,10 @@ def test_projection_forward(cuda, n, c, scale):
     assert int(g_counts[..., 0].sum()) == int(tiles_ref.sum())
 
 
-# the scatter picks its chunk by launch size: 64 (first two), 256 (20000 x 1, 3000 x 8), 2048 (140000 x 1)
+# the scatter picks its chunk by launch size: 32 (4000 x 1, 1500 x 4, 5 x 9), 64 (9000 x 1),
+# 256 (20000 x 1, 3000 x 8), 2048 (140000 x 1)
 @pytest.mark.parametrize("n,c,scale", [(4000, 1, 0.5), (1500, 4, 0.25), (0, 1, 0.25), (5, 9, 0.25),
-                                       (20000, 1, 0.25), (3000, 8, 0.2), (140000, 1, 0.1)])
+                                       (9000, 1, 0.25), (20000, 1, 0.25), (3000, 8, 0.2), (140000, 1, 0.1)])
 def test_isect_bit_exact(cuda, n, c, scale):
     """Counts, sorted keys, values and tile ranges are bit-exact on identical projected inputs."""
     sc = make_scene(max(n, 1), c, "tum", scale)
