@@ -10,7 +10,7 @@ capacity; results of an overflowed replay are incomplete.
 """
 from __future__ import annotations
 
-from typing import Callable
+from typing import Callable, Optional
 
 import torch
 
@@ -18,13 +18,15 @@ from . import _lib, ops
 
 
 class GraphedStep:
-    def __init__(self, fn: Callable[[], torch.Tensor], headroom: float = 1.3, warmup: int = 2):
+    def __init__(self, fn: Callable[[], torch.Tensor], headroom: float = 1.3, warmup: int = 2,
+                 n_isects_hint: Optional[int] = None):
         """`fn()` runs one full step (forward, loss, backward, collectives) on static tensors
         and returns the loss.  It is run eagerly `warmup` times (which also measures the
-        intersection count), then captured."""
+        intersection count), then captured.  A caller that has just run the same step eagerly
+        passes the count it saw as `n_isects_hint` instead, and nothing runs before the capture."""
         assert ops.isect_capacity is None
-        n_max = 0
-        for _ in range(max(warmup, 1)):
+        n_max = int(n_isects_hint or 0)
+        for _ in range(max(warmup, 1) if n_isects_hint is None else 0):
             fn()
             n_max = max(n_max, int(ops.last_n_isects.item()))
         self.capacity = int(n_max * headroom) + 4096

@@ -36,6 +36,7 @@ from torch import Tensor
 
 from .lbfgs import lbfgs_minimize
 from .losses import photometric_ssim_loss
+from .graph import GraphedStep
 from .insertion import InsertFromDepthMap, InsertUsingImagePlaneGradients, KeyframeView
 from .map import GaussianSplattingData
 from .mapping import DEFAULT_LRS, LOCAL, PARAM_NAMES, FlatSplats, MappingStep
@@ -71,6 +72,9 @@ class MapConfig:
     grow_grad2d: float = 0.0002             # InsertUsingImagePlaneGradients(0.0002, 0.01) (:147-150)
     grow_scale3d: float = 0.01
     use_gt_depths: bool = False             # RGB-D mode (:111): depth terms in mapping and tracking
+    graph_mapping: bool = True              # replay rounds of >= graph_min_iters iterations as a CUDA graph
+    graph_min_iters: int = 10
+    graph_check_every: int = 5
     optimize_poses: bool = True             # optimize_poses_lbfgs after every idle mapping round (:851)
 
 
@@ -82,6 +86,26 @@ class Keyframe:
     exposure: Tensor            # [2], fixed once the frame is a keyframe (:660-662)
     est_depths: Optional[Tensor] = None
     gt_depth: Optional[Tensor] = None
+
+
+@dataclass
+class _Window:
+    """The static tensors of one optimize_map round."""
+    poses: List[PoseZhou]
+    gt: Tensor
+    exposure: Tensor
+    Ks: Tensor
+    gt_depths: Optional[Tensor]
+
+
+@dataclass
+class _MappingGraph:
+    g: GraphedStep
+    res: object                  # MappingStepResult whose tensors every replay rewrites
+    ring: Tensor                 # photometric loss of replay i at ring[i % 64]
+    pos: Tensor
+    pose_grads: list             # [(parameter, graph-owned gradient tensor)]
+    count: int = 0
 
 
 @dataclass
@@ -130,7 +154,7 @@ class Slam:
         self.splats = FlatSplats(empty)
         # one optimizer, one group per parameter: the reference's six Adam instances (:565-590)
         self.opt = FusedAdam([{"params": [p], "lr": DEFAULT_LRS[name]}
-                              for p, name in zip(self.splats.params, PARAM_NAMES)])
+                              for p, name in zip(self.splats.params, PARAM_NAMES)], capturable=True)
         self.pose_opt: Optional[FusedAdam] = None
         self.step = MappingStep(self.splats, self.opt, ssim_weight=c.ssim_weight,
                                 isotropic_weight=c.isotropic_regularization_weight,
@@ -210,56 +234,140 @@ class Slam:
         keys = sorted(self.keyframes)[-self.conf.optim_window_last_n_keyframes:]
         return [self.keyframes[k] for k in keys]
 
+    def _mapping_iteration(self, w: "_Window", densify: bool):
+        """One iteration of the optimize_map loop body (gslam/backend.py:258-359), eagerly."""
+        c = self.conf
+        for p in w.poses:
+            p.dR.grad = None
+            p.dt.grad = None
+        self.step.retain_means2d_grad = densify
+        res = self.step(pose_batch(w.poses), w.Ks, w.gt, w.exposure, self.camera.width, self.camera.height,
+                        len(w.poses), step_optimizer=not densify, gt_depths=w.gt_depths)
+        changed = False
+        if densify:
+            # the reference densifies between backward and the optimizer step (:328-351): the
+            # parameters it re-creates carry no gradient, so that iteration takes no splat step and
+            # only the opacity decay applies (radii padded with zeros for the new rows)
+            n_dup, n_split = self.insertion_3dgs.step(self.splats, self.opt, res.outputs, self.gen)
+            self.stats.inserted += n_dup + n_split
+            self.stats.densified += n_dup + n_split
+            changed = n_dup + n_split > 0
+            if changed:
+                with torch.no_grad():
+                    seen_twice = (res.outputs.radii > 0).sum(dim=0) > 1
+                    self.splats.params[3].mul_(torch.where(seen_twice, c.opacity_decay, 1.0))
+                    res.radii = res.outputs.radii
+                    res.n_touched = torch.cat([res.n_touched, res.n_touched.new_zeros(
+                        res.n_touched.shape[0], n_dup + n_split)], dim=1)
+            else:
+                self.opt.step(decay_param=self.splats.params[3], vis_count=res.vis_count, decay=c.opacity_decay)
+        if self.pose_opt is not None:
+            self.pose_opt.step()            # keyframe 0 is in no group: its pose stays fixed (:604-611)
+        return res, changed
+
+    def _capture_mapping(self, w: "_Window") -> "_MappingGraph":
+        """The iteration above (without densification) as one CUDA graph over the window's static
+        tensors; the photometric loss of every replay goes to a device ring, the pose gradients stay
+        in graph-owned buffers that the (eager, per-keyframe step count) pose optimizer reads."""
+        from . import ops
+        ring = torch.zeros(64, device=self.dev)
+        pos = torch.zeros((), dtype=torch.long, device=self.dev)
+        box = {}
+
+        def fn():
+            for p in w.poses:
+                p.dR.grad = None
+                p.dt.grad = None
+            self.step.retain_means2d_grad = False
+            res = self.step(pose_batch(w.poses), w.Ks, w.gt, w.exposure, self.camera.width, self.camera.height,
+                            len(w.poses), gt_depths=w.gt_depths)
+            with torch.no_grad():
+                ring.index_copy_(0, pos.view(1) % ring.shape[0], res.photometric.detach().view(1))
+                pos.add_(1)
+            box["res"] = res
+            return res.total
+
+        g = GraphedStep(fn, headroom=1.5, n_isects_hint=int(ops.last_n_isects.item()))
+        grads = [(q, q.grad) for p in w.poses for q in (p.dR, p.dt)]
+        return _MappingGraph(g, box["res"], ring, pos, grads)
+
     def optimize_map(self, n_iters: Optional[int] = None, prune: bool = True, regularize: bool = True) -> None:
-        """Backend.optimize_map (gslam/backend.py:248-409)."""
+        """Backend.optimize_map (gslam/backend.py:248-409).
+
+        Rounds of `graph_min_iters` or more iterations are replayed as a CUDA graph after the first
+        (eager) one: the map size and the window are fixed inside a round, so the ~50 launches of an
+        iteration and its two host syncs (intersection count, loss read-back) collapse to one launch.
+        The reference reads the loss every iteration for StopOnPlateau(3, 0.012); the replayed
+        iterations are checked in chunks of `graph_check_every`, so a stop can come that many minus
+        one iterations late.  Densification iterations (every 200th) always run eagerly."""
         c = self.conf
         n_iters = c.num_iters_mapping if n_iters is None else n_iters
         stopper = StopOnPlateau(3, 0.012)
         self.step.tv_w = c.depth_regularization_weight if regularize else 0.0
-        W, H = self.camera.width, self.camera.height
-        res, window = None, self.optimization_window()
-        gt = torch.stack([k.img for k in window])
-        exposure = torch.stack([k.exposure for k in window])
-        Ks = self.camera.intrinsics.expand(len(window), 3, 3).contiguous()
-        poses = [k.pose for k in window]
-        gt_depths = torch.stack([k.gt_depth for k in window]) if c.use_gt_depths else None
-        for _ in range(n_iters):
-            self.total_step += 1
-            for p in poses:
-                p.dR.grad = None
-                p.dt.grad = None
-            densify = c.densify_every > 0 and self.total_step % c.densify_every == 0
-            self.step.retain_means2d_grad = densify
-            res = self.step(pose_batch(poses), Ks, gt, exposure, W, H, len(window), step_optimizer=not densify,
-                            gt_depths=gt_depths)
-            if densify:
-                # the reference densifies between backward and the optimizer step (:328-351): the
-                # parameters it re-creates carry no gradient, so that iteration takes no splat step and
-                # only the opacity decay applies (radii padded with zeros for the new rows)
-                n_dup, n_split = self.insertion_3dgs.step(self.splats, self.opt, res.outputs, self.gen)
-                self.stats.inserted += n_dup + n_split
-                self.stats.densified += n_dup + n_split
-                prune = False
-                if n_dup + n_split:
-                    with torch.no_grad():
-                        seen_twice = (res.outputs.radii > 0).sum(dim=0) > 1
-                        opac = self.splats.params[3]
-                        opac.mul_(torch.where(seen_twice, c.opacity_decay, 1.0))
-                        res.radii = res.outputs.radii
-                        res.n_touched = torch.cat([res.n_touched, res.n_touched.new_zeros(
-                            res.n_touched.shape[0], n_dup + n_split)], dim=1)
-                else:
-                    self.opt.step(decay_param=self.splats.params[3], vis_count=res.vis_count, decay=c.opacity_decay)
-            if self.pose_opt is not None:
-                self.pose_opt.step()            # keyframe 0 is in no group: its pose stays fixed (:604-611)
+        window = self.optimization_window()
+        w = _Window([k.pose for k in window], torch.stack([k.img for k in window]),
+                    torch.stack([k.exposure for k in window]),
+                    self.camera.intrinsics.expand(len(window), 3, 3).contiguous(),
+                    torch.stack([k.gt_depth for k in window]) if c.use_gt_depths else None)
+        for k in self.keyframes.values():            # pose_optimizer.zero_grad() (:265): nothing stale steps
+            k.pose.dR.grad = None
+            k.pose.dt.grad = None
+        use_graph = c.graph_mapping and n_iters >= c.graph_min_iters
+        graph: Optional[_MappingGraph] = None
+        res, done, stopped = None, 0, False
+
+        def account(photo: float) -> bool:
             self.stats.mapping_iters += 1
-            photo = float(res.photometric)      # the reference's per-iteration .item() (:338-349)
             self.stats.last_photometric = photo
             if self.stats.mapping_iters == 1:
                 self.stats.first_photometric = photo
-            if stopper.stop(photo):
-                self.pause_map_optim = True
-                break
+            return stopper.stop(photo)
+
+        def until_densify() -> int:
+            if c.densify_every <= 0:
+                return 1 << 30
+            return c.densify_every - 1 - (self.total_step % c.densify_every)
+
+        while done < n_iters and not stopped:
+            chunk = min(c.graph_check_every, n_iters - done, until_densify()) if use_graph and done > 0 else 0
+            if chunk <= 0:
+                self.total_step += 1
+                densify = c.densify_every > 0 and self.total_step % c.densify_every == 0
+                res, changed = self._mapping_iteration(w, densify)
+                if densify:
+                    prune = False
+                    if changed:
+                        graph = None
+                done += 1
+                stopped = account(float(res.photometric))      # the reference's per-iteration .item() (:338-349)
+                continue
+            if graph is None:
+                graph = self._capture_mapping(w)
+            start = graph.count
+            for _ in range(chunk):
+                graph.g.replay()
+                if self.pose_opt is not None:
+                    for q, gr in graph.pose_grads:
+                        q.grad = gr
+                    self.pose_opt.step()
+            graph.count += chunk
+            self.total_step += chunk
+            done += chunk
+            res = graph.res
+            losses = graph.ring.tolist()                        # the chunk's one sync
+            if int(graph.g.overflow.item()) != 0:
+                # more intersections than the captured buffers hold: the replayed iterations rendered
+                # a truncated image; from here on iterate eagerly (exact buffers)
+                use_graph, graph = False, None
+            for i in range(start, start + chunk):
+                if account(losses[i % len(losses)]):
+                    stopped = True
+                    break
+        if stopped:
+            self.pause_map_optim = True
+        for k in self.keyframes.values():
+            k.pose.dR.grad = None
+            k.pose.dt.grad = None
         if res is None:
             return
         with torch.no_grad():
