@@ -265,6 +265,17 @@ class Slam:
             self.pose_opt.step()            # keyframe 0 is in no group: its pose stays fixed (:604-611)
         return res, changed
 
+    @staticmethod
+    def _light(res):
+        """What the end of a round reads from an iteration's result, detached: holding the live
+        RasterizationOutput would keep its autograd graph -- and the AccumulateGrad nodes of the
+        parameters, which remember the stream they were created on -- alive into the next capture
+        (cudaErrorStreamCaptureImplicit)."""
+        from types import SimpleNamespace
+        from .mapping import MappingStepResult
+        return MappingStepResult(res.total.detach(), res.photometric.detach(), res.radii, res.n_touched,
+                                 res.vis_count, SimpleNamespace(depthmaps=res.outputs.depthmaps.detach()))
+
     def _capture_mapping(self, w: "_Window") -> "_MappingGraph":
         """The iteration above (without densification) as one CUDA graph over the window's static
         tensors; the photometric loss of every replay goes to a device ring, the pose gradients stay
@@ -284,8 +295,8 @@ class Slam:
             with torch.no_grad():
                 ring.index_copy_(0, pos.view(1) % ring.shape[0], res.photometric.detach().view(1))
                 pos.add_(1)
-            box["res"] = res
-            return res.total
+            box["res"] = self._light(res)
+            return box["res"].total
 
         g = GraphedStep(fn, headroom=1.5, n_isects_hint=int(ops.last_n_isects.item()))
         grads = [(q, q.grad) for p in w.poses for q in (p.dR, p.dt)]
@@ -334,6 +345,7 @@ class Slam:
                 self.total_step += 1
                 densify = c.densify_every > 0 and self.total_step % c.densify_every == 0
                 res, changed = self._mapping_iteration(w, densify)
+                res = self._light(res)
                 if densify:
                     prune = False
                     if changed:
