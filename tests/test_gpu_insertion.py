@@ -113,7 +113,7 @@ def test_first_insertion_into_an_empty_map_uses_neighbour_distances(cuda):
                      generator=torch.Generator(device=cuda).manual_seed(3))
     assert added == 500 == splats.n
     means, scales = splats.params[0].detach(), torch.exp(splats.params[2].detach())
-    d = torch.cdist(means, means)
+    d = torch.cdist(means, means, compute_mode="donot_use_mm_for_euclid_dist")
     ref = d.topk(4, largest=False).values[:, 1:].mean(dim=1)
     assert torch.allclose(knn_mean_distance(means, 3), ref, rtol=1e-5, atol=1e-7)
     assert torch.allclose(scales, ref.clamp_min(1e-6)[:, None].expand(500, 3), rtol=1e-4)
