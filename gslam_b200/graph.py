@@ -17,6 +17,18 @@ import torch
 from . import _lib, ops
 
 
+_streams: dict = {}
+
+
+def _capture_stream(device) -> torch.cuda.Stream:
+    """One capture stream per device for the whole process (autograd's AccumulateGrad nodes remember
+    the stream they first ran on; a fresh stream per capture would trip their stream check)."""
+    key = torch.device(device).index
+    if key not in _streams:
+        _streams[key] = torch.cuda.Stream(device=device)
+    return _streams[key]
+
+
 class GraphedStep:
     def __init__(self, fn: Callable[[], torch.Tensor], headroom: float = 1.3, warmup: int = 2,
                  n_isects_hint: Optional[int] = None):
@@ -35,8 +47,20 @@ class GraphedStep:
         launches0 = _lib.launch_count
         ops.isect_capacity = self.capacity
         try:
-            with torch.cuda.graph(self.graph):
-                self.loss = fn()
+            # capture_begin / capture_end on a side stream, i.e. `with torch.cuda.graph(...)` without its
+            # gc.collect() + empty_cache(): a sequence re-captures the mapping step after every map
+            # change, and emptying the allocator cache each time made every following allocation a
+            # cudaMalloc (measured: 40-70 ms per capture inside a long-lived process)
+            cur = torch.cuda.current_stream()
+            side = _capture_stream(cur.device)
+            side.wait_stream(cur)
+            with torch.cuda.stream(side):
+                self.graph.capture_begin()
+                try:
+                    self.loss = fn()
+                finally:
+                    self.graph.capture_end()
+            cur.wait_stream(side)
             self.overflow = ops.last_overflow
             self.n_isects = ops.last_n_isects
         finally:
