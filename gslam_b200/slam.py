@@ -409,47 +409,76 @@ class Slam:
         tolerance_change 1e-7, lr 1) over the window's poses except keyframe 0, objective = the
         photometric part of the mapping loss on the frozen map.  The 9 W unknowns live on the host
         (gslam_b200.lbfgs); an evaluation is one upload, one render + loss + backward to the poses
-        (no gradient to the map, which the reference computes and discards) and one download."""
+        (no gradient to the map, which the reference computes and discards) and one download --
+        after the first, one CUDA-graph launch."""
         window = self.optimization_window()
         free = [k for k in window if k.index != 0]
         if not free:
             return None
+        from . import ops
+        from .primitives import pose_chain
         W, H = self.camera.width, self.camera.height
         gt = torch.stack([k.img for k in window])
         exposure = torch.stack([k.exposure for k in window])
         Ks = self.camera.intrinsics.expand(len(window), 3, 3).contiguous()
-        poses = [k.pose for k in window]
         P = [p.detach() for p in self.splats.params]
         bg = self.bg1.expand(len(window), 3).contiguous()
+        nf = len(free)
+        fixed = [k for k in window if k.index == 0]            # keyframe 0 sorts first in the window
         with torch.no_grad():
-            x0 = torch.cat([torch.cat([k.pose.dR, k.pose.dt]) for k in free]).cpu().numpy()
+            Rt_all = torch.stack([k.pose.Rt for k in window])
+            x0_dev = torch.cat([torch.cat([k.pose.dR, k.pose.dt]) for k in free])
+            fixed_dR = torch.stack([k.pose.dR.detach() for k in fixed]) if fixed else None
+            fixed_dt = torch.stack([k.pose.dt.detach() for k in fixed]) if fixed else None
+        theta = torch.zeros(9 * nf, device=self.dev, requires_grad=True)
+        result = torch.zeros(1 + 9 * nf, device=self.dev)
+        theta_host = x0_dev.cpu().pin_memory()
+        result_host = torch.zeros(1 + 9 * nf).pin_memory()
+        theta_np, result_np = theta_host.numpy(), result_host.numpy()
+        stream = torch.cuda.current_stream(self.dev)
 
-        def scatter(x) -> None:
-            th = torch.from_numpy(np.asarray(x, dtype=np.float32)).to(self.dev)
+        def fn():
             with torch.no_grad():
-                for i, k in enumerate(free):
-                    k.pose.dR.copy_(th[9 * i:9 * i + 6])
-                    k.pose.dt.copy_(th[9 * i + 6:9 * i + 9])
-
-        def evaluate(x):
-            scatter(x)
-            for k in free:
-                k.pose.dR.grad = None
-                k.pose.dt.grad = None
-            out = rasterization(P[0], P[1], P[2], P[3], P[4], pose_batch(poses), Ks, W, H, packed=False,
+                theta.copy_(theta_host, non_blocking=True)
+            theta.grad = None
+            th = theta.view(nf, 9)
+            dR, dt = th[:, :6], th[:, 6:]
+            if fixed:
+                dR, dt = torch.cat([fixed_dR, dR]), torch.cat([fixed_dt, dt])
+            out = rasterization(P[0], P[1], P[2], P[3], P[4], pose_chain(Rt_all, dR, dt), Ks, W, H, packed=False,
                                 render_mode="RGB+D", log_uncertainties=P[5], backgrounds=bg)
             total, _ = photometric_ssim_loss(out.render, gt, exposure, 0.0, "mapping")
             total.backward()
-            packed = torch.cat([total.detach().view(1)] + [t for k in free for t in (k.pose.dR.grad, k.pose.dt.grad)])
-            r = packed.cpu().numpy()                       # the evaluation's one sync
-            self.stats.pose_lbfgs_evals += 1
-            return float(r[0]), r[1:]
+            torch.cat([total.detach().view(1), theta.grad], out=result)
+            result_host.copy_(result, non_blocking=True)
+            return total.detach()
 
-        res = lbfgs_minimize(evaluate, x0, lr=1.0, max_iter=20, tolerance_change=1e-7, history_size=10)
-        scatter(res.x)
-        for k in free:
-            k.pose.dR.grad = None
-            k.pose.dt.grad = None
+        graph: List[GraphedStep] = []
+
+        def evaluate(x):
+            theta_np[:] = x
+            if not graph:
+                # the first evaluation runs eagerly and sizes the key buffers of the capture; later
+                # ones are one graph launch (upload, render + loss + backward to the poses, download)
+                fn()
+                stream.synchronize()
+                first = float(result_np[0]), result_np[1:].copy()
+                graph.append(GraphedStep(fn, headroom=1.5, n_isects_hint=int(ops.last_n_isects.item())))
+                self.stats.pose_lbfgs_evals += 1
+                return first
+            graph[0].replay()
+            stream.synchronize()                           # the evaluation's one sync
+            self.stats.pose_lbfgs_evals += 1
+            return float(result_np[0]), result_np[1:]
+
+        res = lbfgs_minimize(evaluate, theta_np.copy(), lr=1.0, max_iter=20, tolerance_change=1e-7, history_size=10)
+        overflowed = bool(graph) and int(graph[0].overflow.item()) != 0
+        with torch.no_grad():
+            # an overflowed replay rendered a truncated image: keep the poses the round started from
+            th = x0_dev if overflowed else torch.from_numpy(np.asarray(res.x, dtype=np.float32)).to(self.dev)
+            for i, k in enumerate(free):
+                k.pose.dR.copy_(th[9 * i:9 * i + 6])
+                k.pose.dt.copy_(th[9 * i + 6:9 * i + 9])
         return res.last_loss
 
     def sync(self) -> None:
