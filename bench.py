@@ -568,19 +568,20 @@ def run_ours(args):
     if not args.no_mapping:
         mapping = mapping_leg(args, dev, rank, world)
     closure = tracking_closure_leg(args, dev) if rank == 0 else None
+    import traceback
     track_frames = slam_seq = None
     if rank == 0 and not args.no_sequence:
         # secondary legs: a failure here is reported in place and must not take the headline line down
         try:
             track_frames = tracking_frames_leg(args, dev)
         except Exception as e:   # noqa: BLE001
-            track_frames = {"error": f"{type(e).__name__}: {e}"}
+            track_frames = {"error": f"{type(e).__name__}: {e}", "where": traceback.format_exc().splitlines()[-12:]}
         slam_seq = {}
         for mode, rgbd in (("rgbd", True), ("monocular", False)):
             try:
                 slam_seq[mode] = slam_sequence_leg(args, dev, rgbd)
             except Exception as e:   # noqa: BLE001
-                slam_seq[mode] = {"error": f"{type(e).__name__}: {e}"}
+                slam_seq[mode] = {"error": f"{type(e).__name__}: {e}", "where": traceback.format_exc().splitlines()[-12:]}
 
     if rank == 0:
         hbm, which, sm_max = peaks()

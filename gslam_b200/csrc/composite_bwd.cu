@@ -271,7 +271,8 @@ GSB_API int gsb_composite_bwd(const float* rec, const int32_t* flatten_ids, cons
     (void)N;
     GSB_CHECK_ARG(C >= 0 && width > 0 && height > 0 && tile_w > 0 && tile_h > 0);
     if (C == 0 || n_isects == 0) return 0;
-    GSB_CHECK_ARG(rec && flatten_ids && offsets && render_alphas && last_ids && v_render && v_rec);
+    // flatten_ids may be NULL only when it holds nothing (device-side count, capacity 0: every range is empty)
+    GSB_CHECK_ARG(rec && (flatten_ids || n_isects == -1) && offsets && render_alphas && last_ids && v_render && v_rec);
     GSB_CHECK_ARG(n_isects < ((int64_t)1 << 31));
     GSB_CHECK_ARG(tile_w == (width + GSB_TILE - 1) / GSB_TILE && tile_h == (height + GSB_TILE - 1) / GSB_TILE);
     const int64_t n_lin64 = (int64_t)C * tile_w * tile_h;

@@ -310,6 +310,14 @@ def test_culling_and_empty(cuda):
     assert (o.alphas == 0).all() and (o.depthmaps == 0).all()
     torch.testing.assert_close(o.rgbs, bg.view(1, 1, 1, 3).expand_as(o.rgbs))
     torch.testing.assert_close(o.betas, torch.full_like(o.betas, math.e))
+    # ... and its backward is all zeros (a tracker whose line search looks away from the map gets here)
+    ps = [p.clone().requires_grad_(True) for p in g.params()]
+    vm = g.viewmats.clone().requires_grad_(True)
+    o = rasterization(ps[0], ps[1], ps[2], ps[3], ps[4], vm, g.Ks, g.width, g.height, packed=False,
+                      backgrounds=bg, render_mode="RGB+D", log_uncertainties=ps[5])
+    (o.render.square().sum() + o.alphas.sum()).backward()
+    assert all(p.grad is None or float(p.grad.abs().max()) == 0.0 for p in ps)
+    assert vm.grad is None or float(vm.grad.abs().max()) == 0.0
 
 
 def test_packed_projection(cuda):
