@@ -5,7 +5,7 @@ sizes the key buffers (upstream gsplat has the same sync inside isect_tiles).
 Under capture the buffers get a fixed capacity instead and the kernels read the
 count from device memory, so the whole step replays with one launch.  If a
 replay ever produces more intersections than the capacity, `overflow` (a device
-flag) is non-zero for that replay and the caller must re-capture with a larger
+flag, sticky until `reset_overflow()`) is non-zero from that replay on and the caller must re-capture with a larger
 capacity; results of an overflowed replay are incomplete.
 """
 from __future__ import annotations
@@ -42,6 +42,7 @@ class GraphedStep:
             fn()
             n_max = max(n_max, int(ops.last_n_isects.item()))
         self.capacity = int(n_max * headroom) + 4096
+        self.overflow = torch.zeros(1, dtype=torch.int32, device=ops.last_n_isects.device)
         torch.cuda.synchronize()
         self.graph = torch.cuda.CUDAGraph()
         launches0 = _lib.launch_count
@@ -58,10 +59,12 @@ class GraphedStep:
                 self.graph.capture_begin()
                 try:
                     self.loss = fn()
+                    # every rasterization() call starts from a cleared flag, so the flag of a replay is
+                    # gone with the next one: keep a sticky copy that only reset_overflow() clears
+                    torch.maximum(self.overflow, ops.last_overflow, out=self.overflow)
                 finally:
                     self.graph.capture_end()
             cur.wait_stream(side)
-            self.overflow = ops.last_overflow
             self.n_isects = ops.last_n_isects
         finally:
             ops.isect_capacity = None
@@ -70,6 +73,9 @@ class GraphedStep:
     def replay(self) -> torch.Tensor:
         self.graph.replay()
         return self.loss
+
+    def reset_overflow(self) -> None:
+        self.overflow.zero_()
 
     def check(self) -> None:
         if int(self.overflow.item()) != 0:

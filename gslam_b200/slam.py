@@ -119,6 +119,7 @@ class SlamStats:
     pruned: int = 0
     densified: int = 0
     pose_lbfgs_evals: int = 0
+    pose_lbfgs_overflows: int = 0
     t_tracking: float = 0.0
     t_mapping: float = 0.0
     n_splats: int = 0
@@ -453,7 +454,7 @@ class Slam:
             result_host.copy_(result, non_blocking=True)
             return total.detach()
 
-        graph: List[GraphedStep] = []
+        graph: List[Optional[GraphedStep]] = []
 
         def evaluate(x):
             theta_np[:] = x
@@ -466,16 +467,24 @@ class Slam:
                 graph.append(GraphedStep(fn, headroom=1.5, n_isects_hint=int(ops.last_n_isects.item())))
                 self.stats.pose_lbfgs_evals += 1
                 return first
-            graph[0].replay()
-            stream.synchronize()                           # the evaluation's one sync
+            if graph[0] is not None:
+                graph[0].replay()
+                stream.synchronize()                       # the evaluation's sync
+                if int(graph[0].overflow.item()) == 0:
+                    self.stats.pose_lbfgs_evals += 1
+                    return float(result_np[0]), result_np[1:]
+                # a trial pose that sees more intersections than the captured buffers hold: redo it
+                # with exact buffers and stay eager for the rest of this round
+                graph[0] = None
+                self.stats.pose_lbfgs_overflows += 1
+            fn()
+            stream.synchronize()
             self.stats.pose_lbfgs_evals += 1
             return float(result_np[0]), result_np[1:]
 
         res = lbfgs_minimize(evaluate, theta_np.copy(), lr=1.0, max_iter=20, tolerance_change=1e-7, history_size=10)
-        overflowed = bool(graph) and int(graph[0].overflow.item()) != 0
         with torch.no_grad():
-            # an overflowed replay rendered a truncated image: keep the poses the round started from
-            th = x0_dev if overflowed else torch.from_numpy(np.asarray(res.x, dtype=np.float32)).to(self.dev)
+            th = torch.from_numpy(np.asarray(res.x, dtype=np.float32)).to(self.dev)
             for i, k in enumerate(free):
                 k.pose.dR.copy_(th[9 * i:9 * i + 6])
                 k.pose.dt.copy_(th[9 * i + 6:9 * i + 9])

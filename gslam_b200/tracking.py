@@ -278,6 +278,8 @@ class Tracker:
             for t in (self.m, self.v, self.step_no, self.ring_pos):
                 t.zero_()
             self.lr_scale.fill_(1.0)
+        for g in self._graphs.values():
+            g.reset_overflow()
         self.n_evals = 0
         self.n_syncs = 0
 
