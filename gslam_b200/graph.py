@@ -29,13 +29,41 @@ def _capture_stream(device) -> torch.cuda.Stream:
     return _streams[key]
 
 
+_pools: dict = {}
+
+
+def shared_pool(device):
+    """A graph memory pool that outlives the graphs captured into it (a one-kernel keeper graph holds
+    it open).  A sequence loop captures a new graph after every map change; with a private pool each
+    capture cudaMallocs its whole working set again, with this one it takes the blocks the previous
+    graph gave back.  Graphs that share a pool must never replay concurrently -- they all replay on
+    the one stream of the loop."""
+    key = torch.device(device).index
+    if key not in _pools:
+        handle = torch.cuda.graph_pool_handle()
+        keeper = torch.cuda.CUDAGraph()
+        cur = torch.cuda.current_stream(device)
+        side = _capture_stream(device)
+        side.wait_stream(cur)
+        with torch.cuda.stream(side):
+            keeper.capture_begin(pool=handle)
+            try:
+                torch.zeros(1, device=device)
+            finally:
+                keeper.capture_end()
+        cur.wait_stream(side)
+        _pools[key] = (handle, keeper)
+    return _pools[key][0]
+
+
 class GraphedStep:
     def __init__(self, fn: Callable[[], torch.Tensor], headroom: float = 1.3, warmup: int = 2,
-                 n_isects_hint: Optional[int] = None):
+                 n_isects_hint: Optional[int] = None, pool=None):
         """`fn()` runs one full step (forward, loss, backward, collectives) on static tensors
         and returns the loss.  It is run eagerly `warmup` times (which also measures the
         intersection count), then captured.  A caller that has just run the same step eagerly
-        passes the count it saw as `n_isects_hint` instead, and nothing runs before the capture."""
+        passes the count it saw as `n_isects_hint` instead, and nothing runs before the capture.
+        `pool`: a graph memory pool to capture into (see `shared_pool`); default a private one."""
         assert ops.isect_capacity is None
         n_max = int(n_isects_hint or 0)
         for _ in range(max(warmup, 1) if n_isects_hint is None else 0):
@@ -56,7 +84,7 @@ class GraphedStep:
             side = _capture_stream(cur.device)
             side.wait_stream(cur)
             with torch.cuda.stream(side):
-                self.graph.capture_begin()
+                self.graph.capture_begin(pool=pool) if pool is not None else self.graph.capture_begin()
                 try:
                     self.loss = fn()
                     # every rasterization() call starts from a cleared flag, so the flag of a replay is

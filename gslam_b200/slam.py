@@ -36,7 +36,7 @@ from torch import Tensor
 
 from .lbfgs import lbfgs_minimize
 from .losses import photometric_ssim_loss
-from .graph import GraphedStep
+from .graph import GraphedStep, shared_pool
 from .insertion import InsertFromDepthMap, InsertUsingImagePlaneGradients, KeyframeView
 from .map import GaussianSplattingData
 from .mapping import DEFAULT_LRS, LOCAL, PARAM_NAMES, FlatSplats, MappingStep
@@ -299,7 +299,7 @@ class Slam:
             box["res"] = self._light(res)
             return box["res"].total
 
-        g = GraphedStep(fn, headroom=1.5, n_isects_hint=int(ops.last_n_isects.item()))
+        g = GraphedStep(fn, headroom=1.5, n_isects_hint=int(ops.last_n_isects.item()), pool=shared_pool(self.dev))
         grads = [(q, q.grad) for p in w.poses for q in (p.dR, p.dt)]
         return _MappingGraph(g, box["res"], ring, pos, grads)
 
@@ -464,7 +464,8 @@ class Slam:
                 fn()
                 stream.synchronize()
                 first = float(result_np[0]), result_np[1:].copy()
-                graph.append(GraphedStep(fn, headroom=1.5, n_isects_hint=int(ops.last_n_isects.item())))
+                graph.append(GraphedStep(fn, headroom=1.5, n_isects_hint=int(ops.last_n_isects.item()),
+                                         pool=shared_pool(self.dev)))
                 self.stats.pose_lbfgs_evals += 1
                 return first
             if graph[0] is not None:
