@@ -474,11 +474,20 @@ def run_ours(args):
     I = int(out.isect_ids.numel())
     ops.pair_counter = None
     del out
-    _lib.start_timing()
-    for _ in range(min(args.steps, 20)):
-        flush_buf.zero_()
-        step(params, vm, K, gt)
-    kt = _lib.stop_timing()
+    # per-kernel pass: an event pair around every C-ABI call of live steps.  The host must run AHEAD of
+    # the device for such a pair to bracket the kernel alone -- otherwise it also spans the launch
+    # latency of a kernel that reaches an idle GPU (+5 us on every small kernel).  So the key buffers
+    # get a fixed capacity (no mid-step host sync) and each step is queued behind a ~1.5 ms spin kernel.
+    ops.isect_capacity = int(I * 1.3) + 4096
+    try:
+        _lib.start_timing()
+        for _ in range(min(args.steps, 20)):
+            flush_buf.zero_()
+            torch.cuda._sleep(3_000_000)
+            step(params, vm, K, gt)
+        kt = _lib.stop_timing()
+    finally:
+        ops.isect_capacity = None
 
     # ---- e2e: host buffers in, loss + pose gradient out, copies inside the timed region ----------
     h2d = sum(h.numel() * 4 for h in host) + (host_vm.numel() + host_K.numel() + host_gt.numel()) * 4
