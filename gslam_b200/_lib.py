@@ -33,7 +33,8 @@ SIGNATURES = {
     "gsb_tile_scan": (_i, [_p, _i, _i, _i, _p, _p, _p, _p]),
     "gsb_isect_scatter": (_i, [_p, _p, _p, _i, _i, _i, _i, _p, _l, _p, _p, _p]),
     "gsb_segment_sort": (_i, [_p, _p, _p, _i, _i, _i, _i, _l, _p, _p, _p]),
-    "gsb_project_bwd": (_i, [_p] * 8 + [_i, _i, _i, _i, _f] + [_p, _p, _p, _l, _p, _i] + [_p] * 7 + [_p]),
+    "gsb_project_bwd": (_i, [_p] * 8 + [_i, _i, _i, _i, _f] + [_p, _p, _p, _l, _p, _i] + [_p] * 8 + [_p]),
+    "gsb_project_bwd_det_floats": (_z, [_i, _i]),
     "gsb_pack_visible": (_i, [_p] * 4 + [_i, _i] + [_p] * 5 + [_p]),
     "gsb_scan_workspace_bytes": (_z, [_l]),
     "gsb_scan_i32_i64": (_i, [_p, _l, _i, _p, _p, _z, _p]),
@@ -42,14 +43,17 @@ SIGNATURES = {
     "gsb_sort_pairs": (_i, [_p] * 4 + [_l, _i, _p, _z, _p]),
     "gsb_isect_offsets": (_i, [_p, _l, _i, _i, _i, _i, _p, _p]),
     "gsb_composite_fwd": (_i, [_p] * 4 + [_i] * 6 + [_l, _f] + [_p] * 5 + [_p]),
-    "gsb_ssim_fwd": (_i, [_p] * 4 + [_i] * 5 + [_p] * 4 + [_p]),
+    "gsb_ssim_fwd": (_i, [_p] * 4 + [_i] * 5 + [_p] * 5 + [_p]),
+    "gsb_ssim_fwd_det_floats": (_z, [_i, _i, _i, _i]),
     "gsb_ssim_bwd": (_i, [_p] * 4 + [_i] * 4 + [_p] * 4 + [_f, _p, _p, _i, _p]),
-    "gsb_photo_loss": (_i, [_p, _p, _p, _i, _i, _i, _i, _f, _p, _p, _p, _p, _p]),
+    "gsb_photo_loss": (_i, [_p, _p, _p, _i, _i, _i, _i, _f, _p, _p, _p, _p, _p, _p]),
+    "gsb_photo_loss_det_floats": (_z, [_i, _i, _i]),
     "gsb_scale_by_scalar": (_i, [_p, _l, _p, _p]),
     "gsb_adam_multi": (_i, [_p, _i, _f, _f, _f, _i, _i, _p, _i, _f, _p, _p]),
-    "gsb_composite_bwd": (_i, [_p] * 4 + [_i] * 6 + [_l] + [_p] * 6 + [_p]),
+    "gsb_composite_bwd": (_i, [_p] * 4 + [_i] * 6 + [_l] + [_p] * 6 + [_p, _p, _p, _z] + [_p]),
+    "gsb_composite_bwd_det_bytes": (_z, [_l]),
     "gsb_vis_count": (_i, [_p, _i, _l, _p, _p]),
-    "gsb_isotropic_reg": (_i, [_p, _p, _l, _f, _p, _p, _p]),
+    "gsb_isotropic_reg": (_i, [_p, _p, _l, _f, _p, _p, _p, _p]),
     "gsb_rows_resize": (_i, [_p, _i, _l, _p, _l, _l, _p]),
     "gsb_pose_fwd": (_i, [_p, _p, _p, _i, _p, _p]),
     "gsb_pose_bwd": (_i, [_p, _p, _p, _i, _p, _p, _p]),

@@ -29,6 +29,9 @@ void gsb_set_error(const char* fmt, ...);
 
 #define GSB_LAUNCH_CHECK() GSB_CUDA(cudaGetLastError())
 
+// dst[0] = sum of partials[0..n) in a fixed order (loss.cu); the finish of every deterministic-mode reduction
+int gsb_det_sum_launch(const float* partials, int64_t n, float* dst, cudaStream_t st);
+
 static inline cudaStream_t gsb_stream(void* s) { return reinterpret_cast<cudaStream_t>(s); }
 
 __device__ __forceinline__ float warp_sum(float v) {

@@ -43,13 +43,18 @@ __device__ __forceinline__ void sts32(unsigned addr, float v) {
     asm volatile("st.shared.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory");
 }
 
+// DET: instead of three float4 atomics, a finished row goes to det_rows[(q * det_cap + li) * 3] (q: the
+// unit inside its tile, li: the entry's list index) and its bit is set in det_mask; the gather kernel
+// below then sums the rows of every Gaussian in a fixed order (bit-reproducible gradients).
+template <bool DET>
 __global__ void __launch_bounds__(CMP_THREADS)
 composite_bwd_kernel(const float4* __restrict__ rec, const int32_t* __restrict__ flatten_ids,
                      const int32_t* __restrict__ offsets, const float* __restrict__ backgrounds,
                      int n_lin, int width, int height, int tile_w, int tile_h, int64_t n_isects,
                      const float* __restrict__ render_alphas, const int32_t* __restrict__ last_ids,
                      const float* __restrict__ v_render, const float* __restrict__ v_alphas,
-                     float* __restrict__ v_rec, float* __restrict__ v_backgrounds) {
+                     float* __restrict__ v_rec, float* __restrict__ v_backgrounds,
+                     float4* __restrict__ det_rows, unsigned* __restrict__ det_mask, int64_t det_cap) {
     __shared__ WarpStage s_ws[CMP_WARPS];
     __shared__ int32_t s_ids[CMP_WARPS][NSTAGE][RND];
     __shared__ __align__(16) float s_acc[CMP_WARPS][RND][12];
@@ -248,10 +253,17 @@ composite_bwd_kernel(const float4* __restrict__ rec, const int32_t* __restrict__
             a0.w *= 0.5f;            // d sigma / d conic_a = dx^2 / 2
             a1.y *= 0.5f;            // d sigma / d conic_c = dy^2 / 2
             a2.w = 0.f;
-            float4* dst = reinterpret_cast<float4*>(v_rec) + (size_t)ws.gid[lane] * 3;
-            atomicAdd(dst, a0);
-            atomicAdd(dst + 1, a1);
-            atomicAdd(dst + 2, a2);
+            if (DET) {
+                const int64_t row = (int64_t)(unit % UNITS_PER_TILE) * det_cap + __float_as_int(slot[RND + lane].y);
+                float4* dst = det_rows + row * 3;
+                dst[0] = a0; dst[1] = a1; dst[2] = a2;
+                atomicOr(det_mask + (row >> 5), 1u << (row & 31));
+            } else {
+                float4* dst = reinterpret_cast<float4*>(v_rec) + (size_t)ws.gid[lane] * 3;
+                atomicAdd(dst, a0);
+                atomicAdd(dst + 1, a1);
+                atomicAdd(dst + 2, a2);
+            }
         }
         __syncwarp();
         k_base += STAGE_BYTES;
@@ -263,14 +275,131 @@ composite_bwd_kernel(const float4* __restrict__ rec, const int32_t* __restrict__
 #endif
 }
 
+// ---------------------------------------------------------------------------
+// Deterministic accumulation, second half: one thread per (camera, Gaussian) sums the rows the
+// units wrote for it -- its tile rectangle in row-major order, the units of a tile in order -- so the
+// gradient is a fixed-order sum, bit-identical from run to run.  The entry's position in a tile's
+// sorted list is found by a binary search for its depth bits (ties: scan for the flatten id; the
+// list is sorted by (depth bits, flatten id)).  Rectangles above TILES_DIRECT tiles are shared by
+// the warp, partial sums joined by a fixed butterfly.  v_rec is written for every (c, n), so the
+// caller need not zero it.
+// ---------------------------------------------------------------------------
+struct Row12 {
+    float4 a, b, c;
+};
+
+__device__ __forceinline__ void row_add(Row12& r, const float4 a, const float4 b, const float4 c) {
+    r.a.x += a.x; r.a.y += a.y; r.a.z += a.z; r.a.w += a.w;
+    r.b.x += b.x; r.b.y += b.y; r.b.z += b.z; r.b.w += b.w;
+    r.c.x += c.x; r.c.y += c.y; r.c.z += c.z; r.c.w += c.w;
+}
+
+__device__ __forceinline__ void gather_tile(Row12& acc, int lin, uint32_t dbits, int id,
+                                            const int32_t* __restrict__ offsets, int n_lin, int64_t n_isects,
+                                            const int64_t* __restrict__ isect_ids,
+                                            const int32_t* __restrict__ flatten_ids,
+                                            const float4* __restrict__ det_rows,
+                                            const unsigned* __restrict__ det_mask, int64_t det_cap) {
+    const TileRange rg = tile_range(offsets, lin, n_lin, n_isects);
+    int lo = rg.start, hi = rg.end;
+    while (lo < hi) {       // first entry whose depth bits are >= dbits
+        const int mid = (lo + hi) >> 1;
+        if ((uint32_t)isect_ids[mid] < dbits) lo = mid + 1; else hi = mid;
+    }
+    while (lo < rg.end && flatten_ids[lo] != id) {
+        if ((uint32_t)isect_ids[lo] != dbits) return;       // not in this list (clipped by an overflowed capacity)
+        ++lo;
+    }
+    if (lo >= rg.end) return;
+#pragma unroll
+    for (int q = 0; q < UNITS_PER_TILE; ++q) {
+        const int64_t row = (int64_t)q * det_cap + lo;
+        if ((det_mask[row >> 5] >> (row & 31)) & 1u) {
+            const float4* src = det_rows + row * 3;
+            row_add(acc, src[0], src[1], src[2]);
+        }
+    }
+}
+
+__global__ void __launch_bounds__(256)
+composite_bwd_gather_kernel(const float* __restrict__ rec, const int32_t* __restrict__ radii, int64_t CN, int N,
+                            int tile_w, int tile_h, const int32_t* __restrict__ offsets, int n_lin,
+                            int64_t n_isects, const int64_t* __restrict__ isect_ids,
+                            const int32_t* __restrict__ flatten_ids, const float4* __restrict__ det_rows,
+                            const unsigned* __restrict__ det_mask, int64_t det_cap, float4* __restrict__ v_rec) {
+    const unsigned full = 0xffffffffu;
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int lane = threadIdx.x & 31;
+    const int r = (i < CN) ? radii[i] : 0;
+    int x0 = 0, x1 = 0, y0 = 0, y1 = 0, cnt = 0, cam = 0;
+    uint32_t dbits = 0;
+    if (r > 0) {
+        const float4 r0 = reinterpret_cast<const float4*>(rec)[i * 3];
+        tile_bbox(r0.x, r0.y, r, tile_w, tile_h, x0, x1, y0, y1);
+        cnt = (x1 - x0) * (y1 - y0);
+        cam = (int)(i / N);
+        dbits = __float_as_uint(rec[i * GSB_REC + 9]);
+    }
+    const int n_tiles = tile_w * tile_h;
+    const int bw = x1 - x0;
+    Row12 acc;
+    acc.a = acc.b = acc.c = make_float4(0.f, 0.f, 0.f, 0.f);
+    const bool big = cnt > TILES_DIRECT;
+    if (!big) {
+        int tx = x0, ty = y0;
+        for (int t = 0; t < cnt; ++t) {
+            gather_tile(acc, cam * n_tiles + ty * tile_w + tx, dbits, (int)i, offsets, n_lin, n_isects, isect_ids,
+                        flatten_ids, det_rows, det_mask, det_cap);
+            if (++tx == x1) { tx = x0; ++ty; }
+        }
+    }
+    unsigned bigmask = __ballot_sync(full, big);
+    while (bigmask) {
+        const int src = __ffs(bigmask) - 1;
+        bigmask &= bigmask - 1;
+        const int o_x0 = __shfl_sync(full, x0, src), o_y0 = __shfl_sync(full, y0, src);
+        const int o_bw = max(__shfl_sync(full, bw, src), 1), o_cnt = __shfl_sync(full, cnt, src);
+        const int o_cam = __shfl_sync(full, cam, src);
+        const uint32_t o_d = __shfl_sync(full, dbits, src);
+        const int o_id = (int)__shfl_sync(full, (int)i, src);
+        Row12 part;
+        part.a = part.b = part.c = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int t = lane; t < o_cnt; t += 32) {
+            const int dy = t / o_bw;
+            gather_tile(part, o_cam * n_tiles + (o_y0 + dy) * tile_w + o_x0 + (t - dy * o_bw), o_d, o_id, offsets,
+                        n_lin, n_isects, isect_ids, flatten_ids, det_rows, det_mask, det_cap);
+        }
+        float* pf = reinterpret_cast<float*>(&part);
+#pragma unroll
+        for (int k = 0; k < 12; ++k) pf[k] = warp_sum(pf[k]);       // fixed butterfly: same bits in every lane
+        if (lane == src) acc = part;
+    }
+    if (i < CN) {
+        float4* dst = v_rec + i * 3;
+        dst[0] = acc.a; dst[1] = acc.b; dst[2] = acc.c;
+    }
+}
+
+GSB_API size_t gsb_composite_bwd_det_bytes(int64_t capacity) {
+    if (capacity <= 0) return 0;
+    const size_t rows = (size_t)UNITS_PER_TILE * (size_t)capacity;
+    return rows * 48 + ((rows + 31) / 32) * 4 + 16;
+}
+
 GSB_API int gsb_composite_bwd(const float* rec, const int32_t* flatten_ids, const int32_t* offsets,
                               const float* backgrounds, int C, int N, int width, int height, int tile_w,
                               int tile_h, int64_t n_isects, const float* render_alphas,
                               const int32_t* last_ids, const float* v_render, const float* v_alphas,
-                              float* v_rec, float* v_backgrounds, void* stream) {
-    (void)N;
+                              float* v_rec, float* v_backgrounds, const int32_t* radii,
+                              const int64_t* isect_ids, void* det_workspace, size_t det_workspace_bytes,
+                              void* stream) {
     GSB_CHECK_ARG(C >= 0 && width > 0 && height > 0 && tile_w > 0 && tile_h > 0);
-    if (C == 0 || n_isects == 0) return 0;
+    const bool det = det_workspace != nullptr;
+    if (C == 0) return 0;
+    if (n_isects == 0) {
+        if (det && N > 0) GSB_CUDA(cudaMemsetAsync(v_rec, 0, (size_t)C * N * GSB_REC * 4, gsb_stream(stream)));
+        return 0;
+    }
     // flatten_ids may be NULL only when it holds nothing (device-side count, capacity 0: every range is empty)
     GSB_CHECK_ARG(rec && (flatten_ids || n_isects == -1) && offsets && render_alphas && last_ids && v_render && v_rec);
     GSB_CHECK_ARG(n_isects < ((int64_t)1 << 31));
@@ -279,9 +408,35 @@ GSB_API int gsb_composite_bwd(const float* rec, const int32_t* flatten_ids, cons
     GSB_CHECK_ARG(n_lin64 * UNITS_PER_TILE < ((int64_t)1 << 31));
     const int n_lin = (int)n_lin64;
     const int grid = (UNITS_PER_TILE * n_lin + CMP_WARPS - 1) / CMP_WARPS;
-    composite_bwd_kernel<<<grid, CMP_THREADS, 0, gsb_stream(stream)>>>(
-        reinterpret_cast<const float4*>(rec), flatten_ids, offsets, backgrounds, n_lin, width, height,
-        tile_w, tile_h, n_isects, render_alphas, last_ids, v_render, v_alphas, v_rec, v_backgrounds);
+    const float4* r4 = reinterpret_cast<const float4*>(rec);
+    if (!det) {
+        composite_bwd_kernel<false><<<grid, CMP_THREADS, 0, gsb_stream(stream)>>>(
+            r4, flatten_ids, offsets, backgrounds, n_lin, width, height, tile_w, tile_h, n_isects,
+            render_alphas, last_ids, v_render, v_alphas, v_rec, v_backgrounds, nullptr, nullptr, 0);
+        GSB_LAUNCH_CHECK();
+        return 0;
+    }
+    // deterministic accumulation: rows + mask in the caller's workspace, then the fixed-order gather
+    const int64_t cap = n_isects > 0 ? n_isects : -n_isects - 1;
+    GSB_CHECK_ARG(cap > 0 && radii && isect_ids && flatten_ids && v_backgrounds == nullptr);
+    GSB_CHECK_ARG((reinterpret_cast<uintptr_t>(det_workspace) & 15) == 0);
+    if (det_workspace_bytes < gsb_composite_bwd_det_bytes(cap)) {
+        gsb_set_error("gsb_composite_bwd: deterministic workspace of %zu bytes, %zu needed", det_workspace_bytes,
+                      gsb_composite_bwd_det_bytes(cap));
+        return GSB_EWORKSPACE;
+    }
+    const size_t rows = (size_t)UNITS_PER_TILE * (size_t)cap;
+    float4* det_rows = reinterpret_cast<float4*>(det_workspace);
+    unsigned* det_mask = reinterpret_cast<unsigned*>(reinterpret_cast<char*>(det_workspace) + rows * 48);
+    GSB_CUDA(cudaMemsetAsync(det_mask, 0, ((rows + 31) / 32) * 4, gsb_stream(stream)));
+    composite_bwd_kernel<true><<<grid, CMP_THREADS, 0, gsb_stream(stream)>>>(
+        r4, flatten_ids, offsets, backgrounds, n_lin, width, height, tile_w, tile_h, n_isects, render_alphas,
+        last_ids, v_render, v_alphas, v_rec, nullptr, det_rows, det_mask, cap);
+    GSB_LAUNCH_CHECK();
+    const int64_t CN = (int64_t)C * N;
+    composite_bwd_gather_kernel<<<(unsigned)((CN + 255) / 256), 256, 0, gsb_stream(stream)>>>(
+        rec, radii, CN, N, tile_w, tile_h, offsets, n_lin, n_isects, isect_ids, flatten_ids, det_rows, det_mask,
+        cap, reinterpret_cast<float4*>(v_rec));
     GSB_LAUNCH_CHECK();
     return 0;
 }

@@ -49,7 +49,8 @@ __device__ __forceinline__ float block_sum_256(float v, float* red) {
 __global__ void __launch_bounds__(256)
 ssim_fwd_kernel(const float* __restrict__ img1, const float* __restrict__ img2, Strides4 s1, Strides4 s2,
                 int C, int H, int W, int valid, float* __restrict__ ssim_sum,
-                float* __restrict__ dm_dmu1, float* __restrict__ dm_ds1, float* __restrict__ dm_ds12) {
+                float* __restrict__ dm_dmu1, float* __restrict__ dm_ds1, float* __restrict__ dm_ds12,
+                float* __restrict__ det_partials) {
     __shared__ float sx[SH][SXS], sy[SH][SXS];
     __shared__ float hc[5][SH][HCS];
     __shared__ float red[8];
@@ -136,7 +137,26 @@ ssim_fwd_kernel(const float* __restrict__ img1, const float* __restrict__ img2, 
         part += counted ? m : 0.f;
     }
     const float tot = block_sum_256(part, red);
-    if (tid == 0 && tot != 0.f) atomicAdd(ssim_sum, tot);
+    if (tid == 0) {
+        if (det_partials)   // deterministic mode: summed in a fixed order by det_sum_kernel
+            det_partials[((size_t)blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x] = tot;
+        else if (tot != 0.f) atomicAdd(ssim_sum, tot);
+    }
+}
+
+// dst[0] = sum of p[0..n) in a fixed order (one CTA of 256: strided per-thread sums, then the block tree)
+__global__ void __launch_bounds__(256) det_sum_kernel(const float* __restrict__ p, int64_t n, float* __restrict__ dst) {
+    __shared__ float red[8];
+    float s = 0.f;
+    for (int64_t i = threadIdx.x; i < n; i += 256) s += p[i];
+    s = block_sum_256(s, red);
+    if (threadIdx.x == 0) dst[0] = s;
+}
+
+int gsb_det_sum_launch(const float* partials, int64_t n, float* dst, cudaStream_t st) {
+    det_sum_kernel<<<1, 256, 0, st>>>(partials, n, dst);
+    GSB_LAUNCH_CHECK();
+    return 0;
 }
 
 // v_img1[p] (+)= scale * sum_q w(q-p) [ dmu1(q) + 2 x(p) ds1(q) + y(p) ds12(q) ],  scale = *grad * coef
@@ -215,16 +235,22 @@ static Strides4 mk(const int64_t* s) { return Strides4{s[0], s[1], s[2], s[3]}; 
 
 GSB_API int gsb_ssim_fwd(const float* img1, const float* img2, const int64_t* strides1_host,
                          const int64_t* strides2_host, int N, int C, int H, int W, int valid,
-                         float* ssim_sum, float* dm_dmu1, float* dm_ds1, float* dm_ds12, void* stream) {
+                         float* ssim_sum, float* dm_dmu1, float* dm_ds1, float* dm_ds12, float* det_partials,
+                         void* stream) {
     GSB_CHECK_ARG(N >= 0 && C >= 0 && H > 0 && W > 0);
     if (N * C == 0) return 0;
     GSB_CHECK_ARG(img1 && img2 && strides1_host && strides2_host && ssim_sum && N * C <= 65535);
     GSB_CHECK_ARG((dm_dmu1 == nullptr) == (dm_ds1 == nullptr) && (dm_ds1 == nullptr) == (dm_ds12 == nullptr));
     dim3 grid((W + SB - 1) / SB, (H + SB - 1) / SB, N * C);
     ssim_fwd_kernel<<<grid, 256, 0, gsb_stream(stream)>>>(img1, img2, mk(strides1_host), mk(strides2_host), C, H, W,
-                                                          valid, ssim_sum, dm_dmu1, dm_ds1, dm_ds12);
+                                                          valid, ssim_sum, dm_dmu1, dm_ds1, dm_ds12, det_partials);
     GSB_LAUNCH_CHECK();
+    if (det_partials) return gsb_det_sum_launch(det_partials, (int64_t)grid.x * grid.y * grid.z, ssim_sum, gsb_stream(stream));
     return 0;
+}
+
+GSB_API size_t gsb_ssim_fwd_det_floats(int N, int C, int H, int W) {
+    return (size_t)((W + SB - 1) / SB) * ((H + SB - 1) / SB) * (size_t)N * C;
 }
 
 GSB_API int gsb_ssim_bwd(const float* img1, const float* img2, const int64_t* strides1_host,
@@ -256,7 +282,7 @@ __global__ void __launch_bounds__(256)
 photo_loss_kernel(const float* __restrict__ render, const float* __restrict__ gt,
                   const float* __restrict__ exposure, int mode, int HW, float inv_count, float coef,
                   float* __restrict__ loss_sum, float* __restrict__ loss_out, float* __restrict__ v_render,
-                  float* __restrict__ v_exposure) {
+                  float* __restrict__ v_exposure, float* __restrict__ det_partials) {
     __shared__ float red[8];
     // the CTA's 256 pixels pass through shared memory so that global traffic is 16-byte and
     // coalesced; a thread then reads its own pixel at stride 5 / 3 floats (conflict-free)
@@ -342,6 +368,18 @@ photo_loss_kernel(const float* __restrict__ render, const float* __restrict__ gt
     __syncthreads();        // the next chunk overwrites the staging buffers
     }
     float s;
+    if (det_partials) {
+        // deterministic mode: the four block sums go to partials[k][block]; photo_finish_kernel adds them up
+        const size_t nb = (size_t)gridDim.x * gridDim.y, b = (size_t)blockIdx.y * gridDim.x + blockIdx.x;
+        s = block_sum_256(t1, red); if (threadIdx.x == 0) det_partials[b] = s;
+        __syncthreads();
+        s = block_sum_256(t2, red); if (threadIdx.x == 0) det_partials[nb + b] = s;
+        __syncthreads();
+        s = block_sum_256(ga, red); if (threadIdx.x == 0) det_partials[2 * nb + b] = s;
+        __syncthreads();
+        s = block_sum_256(gb, red); if (threadIdx.x == 0) det_partials[3 * nb + b] = s;
+        return;
+    }
     s = block_sum_256(t1, red); if (threadIdx.x == 0 && s != 0.f) atomicAdd(loss_sum, s);
     __syncthreads();
     s = block_sum_256(t2, red); if (threadIdx.x == 0 && s != 0.f) atomicAdd(loss_sum + 1, s);
@@ -365,19 +403,63 @@ photo_loss_kernel(const float* __restrict__ render, const float* __restrict__ gt
     }
 }
 
+// Deterministic finish: block 0 sums the two loss partials over all CTAs, block 1 + c the exposure
+// gradient of camera c over that camera's CTAs; fixed order (strided per-thread sums + the block tree).
+__global__ void __launch_bounds__(256)
+photo_finish_kernel(const float* __restrict__ partials, int gx, int C, float inv_count, float coef,
+                    float* __restrict__ loss_sum, float* __restrict__ loss_out, float* __restrict__ v_exposure) {
+    __shared__ float red[8];
+    const size_t nb = (size_t)gx * C;
+    auto fixed_sum = [&](const float* p, size_t n) -> float {
+        float s = 0.f;
+        for (size_t i = threadIdx.x; i < n; i += 256) s += p[i];
+        __syncthreads();
+        return block_sum_256(s, red);
+    };
+    if (blockIdx.x == 0) {
+        const float a = fixed_sum(partials, nb);
+        const float b = fixed_sum(partials + nb, nb);
+        if (threadIdx.x == 0) {
+            loss_sum[0] = a; loss_sum[1] = b;
+            if (loss_out) { const float photo = (a + b) * inv_count; loss_out[0] = coef * photo; loss_out[1] = photo; }
+        }
+    } else if (v_exposure) {
+        const int cam = blockIdx.x - 1;
+        const float a = fixed_sum(partials + 2 * nb + (size_t)cam * gx, gx);
+        const float b = fixed_sum(partials + 3 * nb + (size_t)cam * gx, gx);
+        if (threadIdx.x == 0) { v_exposure[cam * 2] = a; v_exposure[cam * 2 + 1] = b; }
+    }
+}
+
+static dim3 photo_grid(int C, int H, int W) {
+    const int HW = H * W;
+    const int chunks = (HW + 255) / 256, per_cam = (148 * 4 + C - 1) / C;
+    return dim3(chunks < per_cam ? chunks : per_cam, C);
+}
+
+GSB_API size_t gsb_photo_loss_det_floats(int C, int H, int W) {
+    if (C <= 0 || H <= 0 || W <= 0) return 0;
+    const dim3 g = photo_grid(C, H, W);
+    return (size_t)4 * g.x * g.y;
+}
+
 GSB_API int gsb_photo_loss(const float* render, const float* gt, const float* exposure, int mode, int C,
                            int H, int W, float coef, float* loss_sum, float* loss_out, float* v_render,
-                           float* v_exposure, void* stream) {
+                           float* v_exposure, float* det_partials, void* stream) {
     GSB_CHECK_ARG(C >= 0 && H > 0 && W > 0 && mode >= 0 && mode <= 3);
     if (C == 0) return 0;
     GSB_CHECK_ARG(render && gt && loss_sum && v_render && C <= 65535);
     const int HW = H * W;
-    const int chunks = (HW + 255) / 256, per_cam = (148 * 4 + C - 1) / C;
-    dim3 grid(chunks < per_cam ? chunks : per_cam, C);
-    photo_loss_kernel<<<grid, 256, 0, gsb_stream(stream)>>>(render, gt, exposure, mode, HW,
-                                                            1.0f / ((float)C * (float)HW), coef, loss_sum,
-                                                            loss_out, v_render, v_exposure);
+    const dim3 grid = photo_grid(C, H, W);
+    const float inv_count = 1.0f / ((float)C * (float)HW);
+    photo_loss_kernel<<<grid, 256, 0, gsb_stream(stream)>>>(render, gt, exposure, mode, HW, inv_count, coef, loss_sum,
+                                                            loss_out, v_render, v_exposure, det_partials);
     GSB_LAUNCH_CHECK();
+    if (det_partials) {
+        photo_finish_kernel<<<1 + (v_exposure ? C : 0), 256, 0, gsb_stream(stream)>>>(
+            det_partials, (int)grid.x, C, inv_count, coef, loss_sum, loss_out, v_exposure);
+        GSB_LAUNCH_CHECK();
+    }
     return 0;
 }
 

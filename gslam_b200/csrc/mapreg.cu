@@ -20,7 +20,8 @@ vis_count_kernel(const int32_t* __restrict__ radii, int C, int64_t N, int32_t* _
 // adds dL/ds = weight * sign(e - m) * e to v_log_scales and the UNWEIGHTED sum of |e - m| to *loss_sum.
 __global__ void __launch_bounds__(256)
 isotropic_reg_kernel(const float* __restrict__ log_scales, const int32_t* __restrict__ vis_count,
-                     int64_t N, float weight, float* __restrict__ v_log_scales, float* __restrict__ loss_sum) {
+                     int64_t N, float weight, float* __restrict__ v_log_scales, float* __restrict__ loss_sum,
+                     float* __restrict__ det_partials) {
     __shared__ float red[8];
     const int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     float part = 0.f;
@@ -43,7 +44,8 @@ isotropic_reg_kernel(const float* __restrict__ log_scales, const int32_t* __rest
         float s = 0.f;
 #pragma unroll
         for (int w = 0; w < 8; ++w) s += red[w];
-        if (s != 0.f) atomicAdd(loss_sum, s);
+        if (det_partials) det_partials[blockIdx.x] = s;     // deterministic mode: fixed-order sum afterwards
+        else if (s != 0.f) atomicAdd(loss_sum, s);
     }
 }
 
@@ -57,12 +59,14 @@ GSB_API int gsb_vis_count(const int32_t* radii, int C, int64_t N, int32_t* vis_c
 }
 
 GSB_API int gsb_isotropic_reg(const float* log_scales, const int32_t* vis_count, int64_t N, float weight,
-                              float* v_log_scales, float* loss_sum, void* stream) {
+                              float* v_log_scales, float* loss_sum, float* det_partials, void* stream) {
     GSB_CHECK_ARG(N >= 0);
     if (N == 0) return 0;
     GSB_CHECK_ARG(log_scales && vis_count && v_log_scales);
-    isotropic_reg_kernel<<<(unsigned)((N + 255) / 256), 256, 0, gsb_stream(stream)>>>(
-        log_scales, vis_count, N, weight, v_log_scales, loss_sum);
+    const unsigned blocks = (unsigned)((N + 255) / 256);
+    isotropic_reg_kernel<<<blocks, 256, 0, gsb_stream(stream)>>>(
+        log_scales, vis_count, N, weight, v_log_scales, loss_sum, loss_sum ? det_partials : nullptr);
     GSB_LAUNCH_CHECK();
+    if (loss_sum && det_partials) return gsb_det_sum_launch(det_partials, blocks, loss_sum, gsb_stream(stream));
     return 0;
 }

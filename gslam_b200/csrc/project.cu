@@ -255,7 +255,8 @@ project_bwd_kernel(const float* __restrict__ means, const float* __restrict__ qu
                    const float* __restrict__ v_rec, int need_gauss, float* __restrict__ v_means,
                    float* __restrict__ v_quats, float* __restrict__ v_log_scales,
                    float* __restrict__ v_logit_opac, float* __restrict__ v_logit_colors,
-                   float* __restrict__ v_log_unc, float* __restrict__ v_viewmats) {
+                   float* __restrict__ v_log_unc, float* __restrict__ v_viewmats,
+                   float* __restrict__ det_partials) {
     __shared__ Cam cams[MAX_CAMS_SMEM];
     __shared__ float red[8][12];
     int n = blockIdx.x * blockDim.x + threadIdx.x;
@@ -375,7 +376,9 @@ project_bwd_kernel(const float* __restrict__ means, const float* __restrict__ qu
                     for (int w = 0; w < 8; ++w) acc += red[w][threadIdx.x];
                     int k = threadIdx.x;
                     int slot = (k < 9) ? (k / 3) * 4 + (k % 3) : (k - 9) * 4 + 3;
-                    if (acc != 0.f) atomicAdd(v_viewmats + (size_t)(c0 + ci) * 16 + slot, acc);
+                    if (det_partials)       // deterministic mode: per-block partials, summed in a fixed order below
+                        det_partials[((size_t)(c0 + ci) * 12 + k) * gridDim.x + blockIdx.x] = acc;
+                    else if (acc != 0.f) atomicAdd(v_viewmats + (size_t)(c0 + ci) * 16 + slot, acc);
                 }
                 __syncthreads();
             }
@@ -432,6 +435,23 @@ project_bwd_kernel(const float* __restrict__ means, const float* __restrict__ qu
     }
 }
 
+// Fixed-order sum of the per-block pose-gradient partials [C*12][n_blocks]: one warp per entry, lanes
+// stride over the blocks, a fixed butterfly joins them.  grid C, block 12 * 32.
+__global__ void __launch_bounds__(384)
+viewmat_partials_sum_kernel(const float* __restrict__ partials, int n_blocks, float* __restrict__ v_viewmats) {
+    const int k = threadIdx.x >> 5, lane = threadIdx.x & 31, cam = blockIdx.x;
+    const float* p = partials + ((size_t)cam * 12 + k) * n_blocks;
+    float s = 0.f;
+    for (int b = lane; b < n_blocks; b += 32) s += p[b];
+    s = warp_sum(s);
+    const int slot = (k < 9) ? (k / 3) * 4 + (k % 3) : (k - 9) * 4 + 3;
+    if (lane == 0) v_viewmats[(size_t)cam * 16 + slot] = s;
+}
+
+GSB_API size_t gsb_project_bwd_det_floats(int C, int N) {
+    return (size_t)C * 12 * (size_t)((N + 255) / 256);
+}
+
 GSB_API int gsb_project_bwd(const float* means, const float* quats, const float* log_scales,
                             const float* logit_opacities, const float* logit_colors,
                             const float* log_unc, const float* viewmats, const float* Ks, int C,
@@ -439,7 +459,7 @@ GSB_API int gsb_project_bwd(const float* means, const float* quats, const float*
                             const float* rec, const float* v_means2d, int64_t v_means2d_stride,
                             const float* v_rec, int need_gauss_grads, float* v_means, float* v_quats,
                             float* v_log_scales, float* v_logit_opacities, float* v_logit_colors,
-                            float* v_log_unc, float* v_viewmats, void* stream) {
+                            float* v_log_unc, float* v_viewmats, float* det_partials, void* stream) {
     (void)rec;
     GSB_CHECK_ARG(C >= 0 && N >= 0);
     if (C == 0 || N == 0) return 0;
@@ -451,8 +471,13 @@ GSB_API int gsb_project_bwd(const float* means, const float* quats, const float*
     project_bwd_kernel<<<blocks, 256, 0, gsb_stream(stream)>>>(
         means, quats, log_scales, logit_opacities, logit_colors, log_unc, viewmats, Ks, C, N, width,
         height, eps2d, radii, v_means2d, v_means2d_stride, v_rec, need_gauss_grads, v_means, v_quats,
-        v_log_scales, v_logit_opacities, v_logit_colors, v_log_unc, v_viewmats);
+        v_log_scales, v_logit_opacities, v_logit_colors, v_log_unc, v_viewmats,
+        v_viewmats ? det_partials : nullptr);
     GSB_LAUNCH_CHECK();
+    if (v_viewmats && det_partials) {
+        viewmat_partials_sum_kernel<<<C, 384, 0, gsb_stream(stream)>>>(det_partials, blocks, v_viewmats);
+        GSB_LAUNCH_CHECK();
+    }
     return 0;
 }
 

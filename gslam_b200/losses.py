@@ -15,7 +15,8 @@ from typing import Optional
 import torch
 from torch import Tensor
 
-from ._lib import call, ptr, stream
+from . import ops
+from ._lib import call, lib, ptr, stream
 
 PHOTO_MODES = {"mapping": 0, "active-nerf": 1, "l1": 2, "mse": 3}
 
@@ -34,7 +35,7 @@ def _nchw_like(t: Tensor) -> Tensor:
 
 class _FusedSSIM(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, img1, img2, valid, train):
+    def forward(ctx, img1, img2, valid, train, det=False):
         assert img1.is_cuda and img1.dtype == torch.float32 and img1.dim() == 4 and img1.shape == img2.shape
         N, C, H, W = img1.shape
         if valid and (H <= 10 or W <= 10):
@@ -43,9 +44,10 @@ class _FusedSSIM(torch.autograd.Function):
         ssim_sum = torch.zeros(1, dtype=torch.float32, device=dev)
         need = train and img1.requires_grad
         maps = torch.empty(3, N, C, H, W, dtype=torch.float32, device=dev) if need else None
+        part = ops.det_scratch(lib().gsb_ssim_fwd_det_floats(N, C, H, W), dev) if det else None
         call("gsb_ssim_fwd", ptr(img1), ptr(img2), _strides(img1), _strides(img2), N, C, H, W, int(valid),
              ptr(ssim_sum), ptr(maps[0]) if need else None, ptr(maps[1]) if need else None,
-             ptr(maps[2]) if need else None, stream())
+             ptr(maps[2]) if need else None, ptr(part), stream())
         count = N * C * ((H - 10) * (W - 10) if valid else H * W)
         ctx.save_for_backward(img1, img2, maps)
         ctx.count = count
@@ -62,18 +64,21 @@ class _FusedSSIM(torch.autograd.Function):
         call("gsb_ssim_bwd", ptr(img1), ptr(img2), _strides(img1), _strides(img2), N, C, H, W,
              ptr(maps[0]), ptr(maps[1]), ptr(maps[2]), ptr(g), 1.0 / ctx.count, ptr(v), _strides(v), 0,
              stream())
-        return v, None, None, None
+        return v, None, None, None, None
 
 
-def fused_ssim(img1: Tensor, img2: Tensor, padding: str = "same", train: bool = True) -> Tensor:
-    """Mean SSIM of NCHW images (any strides); gradient to img1 only, like the original."""
+def fused_ssim(img1: Tensor, img2: Tensor, padding: str = "same", train: bool = True,
+               deterministic: Optional[bool] = None) -> Tensor:
+    """Mean SSIM of NCHW images (any strides); gradient to img1 only, like the original.
+    deterministic (extension; None: ops.deterministic): fixed-order sum of the CTA partials."""
     assert padding in ("same", "valid"), padding
-    return _FusedSSIM.apply(img1, img2, padding == "valid", train)
+    det = ops.deterministic if deterministic is None else bool(deterministic)
+    return _FusedSSIM.apply(img1, img2, padding == "valid", train, det)
 
 
 class _PhotometricSSIM(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, render, gt, exposure, ssim_weight, mode, unit_upstream=False):
+    def forward(ctx, render, gt, exposure, ssim_weight, mode, unit_upstream=False, det=False):
         ctx.set_materialize_grads(False)
         # render [C,H,W,5] = (r, g, b, depth, beta); gt [C,H,W,3]; exposure [C,2] or None
         assert render.is_cuda and render.is_contiguous() and render.shape[-1] == 5
@@ -86,8 +91,9 @@ class _PhotometricSSIM(torch.autograd.Function):
         v_render = torch.empty_like(render)
         need_exp = exposure is not None and ctx.needs_input_grad[2]
         v_exp = torch.zeros(C, 2, dtype=torch.float32, device=dev) if need_exp else None
+        part = ops.det_scratch(lib().gsb_photo_loss_det_floats(C, H, W), dev) if det else None
         call("gsb_photo_loss", ptr(render), ptr(gt), ptr(exposure_c), mode, C, H, W, 1.0 - ssim_weight,
-             ptr(loss_sum), ptr(loss_out), ptr(v_render), ptr(v_exp), stream())
+             ptr(loss_sum), ptr(loss_out), ptr(v_render), ptr(v_exp), ptr(part), stream())
         total, photo = loss_out[0], loss_out[1]
         ssim = None
         maps = img1 = img2 = None
@@ -96,8 +102,9 @@ class _PhotometricSSIM(torch.autograd.Function):
             img2 = gt.permute(0, 3, 1, 2)
             ssim_sum = torch.zeros(1, dtype=torch.float32, device=dev)
             maps = torch.empty(3, C, 3, H, W, dtype=torch.float32, device=dev)
+            spart = ops.det_scratch(lib().gsb_ssim_fwd_det_floats(C, 3, H, W), dev) if det else None
             call("gsb_ssim_fwd", ptr(img1), ptr(img2), _strides(img1), _strides(img2), C, 3, H, W, 1,
-                 ptr(ssim_sum), ptr(maps[0]), ptr(maps[1]), ptr(maps[2]), stream())
+                 ptr(ssim_sum), ptr(maps[0]), ptr(maps[1]), ptr(maps[2]), ptr(spart), stream())
             ctx.count = C * 3 * (H - 10) * (W - 10)
             # total + w * (1 - ssim_sum / count) in two launches
             total = torch.sub(total, ssim_sum[0], alpha=ssim_weight / ctx.count) + ssim_weight
@@ -114,7 +121,7 @@ class _PhotometricSSIM(torch.autograd.Function):
         g = g.contiguous()
         if ctx.unit_upstream:
             # the caller calls backward() on this loss itself: the incoming gradient is exactly 1
-            return v_render, None, v_exp, None, None, None
+            return v_render, None, v_exp, None, None, None, None
         call("gsb_scale_by_scalar", ptr(v_render), v_render.numel(), ptr(g), stream())
         if maps is not None:
             img1 = render[..., :3].permute(0, 3, 1, 2)
@@ -123,20 +130,23 @@ class _PhotometricSSIM(torch.autograd.Function):
             call("gsb_ssim_bwd", ptr(img1), ptr(img2), _strides(img1), _strides(img2), C, 3, H, W,
                  ptr(maps[0]), ptr(maps[1]), ptr(maps[2]), ptr(g), -ctx.ssim_weight / ctx.count, ptr(v1),
                  _strides(v1), 1, stream())
-        return v_render, None, (v_exp * g if v_exp is not None else None), None, None, None
+        return v_render, None, (v_exp * g if v_exp is not None else None), None, None, None, None
 
 
 def photometric_ssim_loss(render: Tensor, gt: Tensor, exposure: Optional[Tensor] = None,
-                          ssim_weight: float = 0.2, mode: str = "mapping"):
+                          ssim_weight: float = 0.2, mode: str = "mapping",
+                          deterministic: Optional[bool] = None):
     """(1 - w) * photometric + w * (1 - SSIM_valid)  ->  (total, photometric value).
 
     `render` is the [C,H,W,5] tensor behind RasterizationOutput (rgbs/depthmaps/betas are
     views of it; rasterization() attaches it as ``out.render``)."""
-    return _PhotometricSSIM.apply(render, gt, exposure, float(ssim_weight), PHOTO_MODES[mode])
+    det = ops.deterministic if deterministic is None else bool(deterministic)
+    return _PhotometricSSIM.apply(render, gt, exposure, float(ssim_weight), PHOTO_MODES[mode], False, det)
 
 
 def tracking_loss(render: Tensor, gt: Tensor, exposure: Optional[Tensor] = None,
-                  kind: str = "active-nerf", unit_upstream: bool = False) -> Tensor:
+                  kind: str = "active-nerf", unit_upstream: bool = False,
+                  deterministic: Optional[bool] = None) -> Tensor:
     """gslam/frontend.py:113-129 on the [1,H,W,5] render, exposure = (a, b) as [2] or [1,2].
 
     unit_upstream=True is the caller's promise that the loss reaches `backward()` with coefficient
@@ -145,5 +155,6 @@ def tracking_loss(render: Tensor, gt: Tensor, exposure: Optional[Tensor] = None,
     of multiplying 1.5 M floats by 1.0 in one more pass.  A scaled use of such a loss is WRONG."""
     if exposure is not None and exposure.dim() == 1:
         exposure = exposure.view(1, 2)
-    total, _ = _PhotometricSSIM.apply(render, gt, exposure, 0.0, PHOTO_MODES[kind], unit_upstream)
+    det = ops.deterministic if deterministic is None else bool(deterministic)
+    total, _ = _PhotometricSSIM.apply(render, gt, exposure, 0.0, PHOTO_MODES[kind], unit_upstream, det)
     return total

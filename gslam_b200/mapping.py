@@ -99,9 +99,12 @@ def add_isotropic_grad_(scales_grad: Tensor, log_scales: Tensor, visible: Tensor
     expression below serves the CPU host-logic tests of the mapping step (gloo, stub renderer)."""
     if scales_grad.is_cuda and visible.dtype == torch.int32 and scales_grad.is_contiguous():
         from ._lib import call, ptr, stream
+        from . import ops
         loss = torch.zeros(1, dtype=torch.float32, device=scales_grad.device)
-        call("gsb_isotropic_reg", ptr(log_scales.detach().contiguous()), ptr(visible), log_scales.shape[0],
-             float(weight), ptr(scales_grad), ptr(loss), stream())
+        n = log_scales.shape[0]
+        part = ops.det_scratch((n + 255) // 256, scales_grad.device) if ops.deterministic else None
+        call("gsb_isotropic_reg", ptr(log_scales.detach().contiguous()), ptr(visible), n,
+             float(weight), ptr(scales_grad), ptr(loss), ptr(part), stream())
         return loss[0]
     visible = visible > 0 if visible.dtype != torch.bool else visible
     s = log_scales.detach()

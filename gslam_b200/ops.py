@@ -32,6 +32,39 @@ pair_counter: Optional[Tensor] = None
 grad_tail_floats: int = 0
 
 
+# Deterministic accumulation (bit-identical gradients and loss values from run to run): the float
+# atomics of the backward pass -- v_rec in gsb_composite_bwd, v_viewmats in gsb_project_bwd, the loss
+# and exposure sums of gsb_photo_loss / gsb_ssim_fwd / gsb_isotropic_reg -- are replaced by stored
+# partials summed in a fixed order (include/gsb.h, "Deterministic mode").  Selected per call
+# (`rasterization(..., deterministic=True)`, `photometric_ssim_loss(..., deterministic=True)`, the
+# `deterministic` fields of TrackingConfig / MapConfig) or for a region with `deterministic_mode()`;
+# this module attribute is the default of calls that do not say.
+deterministic: bool = False
+
+
+class deterministic_mode:
+    """`with ops.deterministic_mode(True): ...` -- default of every call inside the block."""
+
+    def __init__(self, flag: bool = True):
+        self.flag = bool(flag)
+
+    def __enter__(self):
+        global deterministic
+        self.prev, deterministic = deterministic, self.flag
+        return self
+
+    def __exit__(self, *exc):
+        global deterministic
+        deterministic = self.prev
+        return False
+
+
+def det_scratch(n_floats: int, device) -> Optional[Tensor]:
+    """Uninitialised scratch for a deterministic-mode reduction (a fresh tensor: under CUDA-graph
+    capture it becomes part of the graph's pool)."""
+    return torch.empty(max(int(n_floats), 1), dtype=torch.float32, device=device)
+
+
 def _c(t: Optional[Tensor]) -> Optional[Tensor]:
     if t is None:
         return None
@@ -49,7 +82,7 @@ class _Project(torch.autograd.Function):
     @staticmethod
     def forward(ctx, means, quats, log_scales, logit_opacities, logit_colors, log_unc, viewmats, Ks,
                 width, height, eps2d, near_plane, far_plane, radius_clip, tile_w, tile_h, tile_counts,
-                sh_degree=None):
+                sh_degree=None, det=False):
         """sh_degree None: logit_colors [N,3] -> sigmoid (the reference).  sh_degree 0..3 (extension):
         logit_colors holds SH coefficients [N,K,3], K >= (sh_degree+1)^2."""
         ctx.set_materialize_grads(False)    # no zero-fill kernels for the integer outputs' "gradients"
@@ -79,6 +112,7 @@ class _Project(torch.autograd.Function):
             ptr(tile_counts), ptr(logit_colors) if sh else None, sh_degree if sh else -1,
             logit_colors.shape[1] if sh else 0, stream())
         ctx.sh_degree = sh_degree
+        ctx.det = bool(det)
         ctx.save_for_backward(means, quats, log_scales, logit_opacities, logit_colors, log_unc,
                               viewmats, Ks, radii, rec)
         ctx.dims = (C, N, width, height, eps2d)
@@ -121,13 +155,17 @@ class _Project(torch.autograd.Function):
             v_means = v_quats = v_scales = v_opac = v_colors = v_unc = None
         v_view = torch.zeros(C, 4, 4, dtype=torch.float32, device=dev) if need_view else None
         sh = ctx.sh_degree is not None
+        det_part = None
+        if ctx.det and need_view:
+            det_part = det_scratch(lib().gsb_project_bwd_det_floats(C, N), dev)
         if need_gauss or need_view:
             call("gsb_project_bwd",
                 ptr(means), ptr(quats), ptr(log_scales), ptr(logit_opacities),
                 None if sh else ptr(logit_colors),
                 ptr(log_unc), ptr(viewmats), ptr(Ks), C, N, width, height, eps2d, ptr(radii), ptr(rec),
                 ptr(g_means2d), m2_stride, ptr(g_rec), int(need_gauss), ptr(v_means), ptr(v_quats),
-                ptr(v_scales), ptr(v_opac), None if sh else ptr(v_colors), ptr(v_unc), ptr(v_view), stream())
+                ptr(v_scales), ptr(v_opac), None if sh else ptr(v_colors), ptr(v_unc), ptr(v_view),
+                ptr(det_part), stream())
         if sh and need_gauss:
             v_colors = torch.empty_like(logit_colors)
             call("gsb_sh_bwd", ptr(means), ptr(logit_colors), ctx.sh_degree, logit_colors.shape[1],
@@ -135,13 +173,13 @@ class _Project(torch.autograd.Function):
         grads = [v_means, v_quats, v_scales, v_opac, v_colors,
                  v_unc if log_unc is not None else None]
         grads = [g if n else None for g, n in zip(grads, need[:6])]
-        return (*grads, v_view, None, None, None, None, None, None, None, None, None, None, None)
+        return (*grads, v_view, None, None, None, None, None, None, None, None, None, None, None, None)
 
 
 class _Composite(torch.autograd.Function):
     @staticmethod
     def forward(ctx, rec, means2d, flatten_ids, offsets, backgrounds, width, height, tile_w, tile_h,
-                visibility_min_T, count_touched, n_touched):
+                visibility_min_T, count_touched, n_touched, det=False, radii=None, isect_ids=None):
         ctx.set_materialize_grads(False)
         # means2d is not read (the record carries x,y); it is an input only so that its
         # gradient is delivered as a separate autograd edge.
@@ -161,7 +199,11 @@ class _Composite(torch.autograd.Function):
             ptr(rec), ptr(flatten_ids), ptr(offsets), ptr(backgrounds), C, N, width, height, tile_w,
             tile_h, n_isects, visibility_min_T, ptr(render), ptr(alphas), ptr(last_ids),
             ptr(n_touched), ptr(pair_counter), stream())
-        ctx.save_for_backward(rec, flatten_ids, offsets, backgrounds, alphas, last_ids)
+        if det and (radii is None or isect_ids is None):
+            raise ValueError("deterministic compositing backward needs radii and isect_ids")
+        ctx.det = bool(det)
+        ctx.save_for_backward(rec, flatten_ids, offsets, backgrounds, alphas, last_ids,
+                              radii if det else None, isect_ids if det else None)
         ctx.dims = (C, N, width, height, tile_w, tile_h, n_isects)
         if n_touched is None:
             n_touched = torch.zeros(C, N, dtype=torch.int64, device=dev)
@@ -170,32 +212,49 @@ class _Composite(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, v_render, v_alphas, _g_touched):
-        rec, flatten_ids, offsets, backgrounds, alphas, last_ids = ctx.saved_tensors
+        rec, flatten_ids, offsets, backgrounds, alphas, last_ids, radii, isect_ids = ctx.saved_tensors
         C, N, width, height, tile_w, tile_h, n_isects = ctx.dims
         dev = rec.device
         if v_render is None:
             v_render = torch.zeros(C, height, width, CH, dtype=torch.float32, device=dev)
         v_render = v_render.contiguous()
         v_alphas = v_alphas.contiguous() if v_alphas is not None else None
-        v_rec = torch.zeros(C, N, REC, dtype=torch.float32, device=dev)
         need_bg = backgrounds is not None and ctx.needs_input_grad[4]
-        v_bg = torch.zeros(C, CH, dtype=torch.float32, device=dev) if need_bg else None
-        call("gsb_composite_bwd", 
-            ptr(rec), ptr(flatten_ids), ptr(offsets), ptr(backgrounds), C, N, width, height, tile_w,
-            tile_h, n_isects, ptr(alphas), ptr(last_ids), ptr(v_render), ptr(v_alphas),
-            ptr(v_rec), ptr(v_bg), stream())
+        cap = flatten_ids.numel()
+        if ctx.det and cap > 0:
+            # rows + fixed-order gather: v_rec is written for every (c, n), nothing to zero
+            v_rec = torch.empty(C, N, REC, dtype=torch.float32, device=dev)
+            nbytes = lib().gsb_composite_bwd_det_bytes(cap)
+            ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+            v_bg = None
+            call("gsb_composite_bwd",
+                 ptr(rec), ptr(flatten_ids), ptr(offsets), ptr(backgrounds), C, N, width, height, tile_w,
+                 tile_h, n_isects, ptr(alphas), ptr(last_ids), ptr(v_render), ptr(v_alphas),
+                 ptr(v_rec), None, ptr(radii), ptr(isect_ids), ptr(ws), nbytes, stream())
+            if need_bg:     # sum_pixels (1 - alpha) v_render: a plain (deterministic) torch reduction
+                v_bg = ((1.0 - alphas) * v_render).sum(dim=(1, 2))
+        else:
+            v_rec = torch.zeros(C, N, REC, dtype=torch.float32, device=dev)
+            v_bg = torch.zeros(C, CH, dtype=torch.float32, device=dev) if need_bg else None
+            call("gsb_composite_bwd",
+                 ptr(rec), ptr(flatten_ids), ptr(offsets), ptr(backgrounds), C, N, width, height, tile_w,
+                 tile_h, n_isects, ptr(alphas), ptr(last_ids), ptr(v_render), ptr(v_alphas),
+                 ptr(v_rec), ptr(v_bg), None, None, None, 0, stream())
         # x,y gradients travel on the means2d edge; _Project.backward ignores those two slots of v_rec
-        return v_rec, v_rec[..., 0:2], None, None, v_bg, None, None, None, None, None, None, None
+        return (v_rec, v_rec[..., 0:2], None, None, v_bg, None, None, None, None, None, None, None,
+                None, None, None)
 
 
 def project(means, quats, log_scales, logit_opacities, logit_colors, log_unc, viewmats, Ks, width,
             height, eps2d=0.3, near_plane=0.01, far_plane=1e10, radius_clip=0.0, tile_counts=None,
-            sh_degree=None):
-    """tile_counts: optional pre-zeroed int32 [C, T, 32] (see ZeroPool)."""
+            sh_degree=None, det=None):
+    """tile_counts: optional pre-zeroed int32 [C, T, 32] (see ZeroPool); det: deterministic backward
+    (None: the module default `deterministic`)."""
     tile_w, tile_h = math.ceil(width / TILE), math.ceil(height / TILE)
     return _Project.apply(means, quats, log_scales, logit_opacities, logit_colors, log_unc, viewmats,
                           Ks, int(width), int(height), float(eps2d), float(near_plane),
-                          float(far_plane), float(radius_clip), tile_w, tile_h, tile_counts, sh_degree)
+                          float(far_plane), float(radius_clip), tile_w, tile_h, tile_counts, sh_degree,
+                          deterministic if det is None else bool(det))
 
 
 class ZeroPool:
@@ -317,11 +376,14 @@ def bin_tiles(means2d, radii, rec, tile_counts, tile_w, tile_h, overflow=None):
 
 
 def composite(rec, means2d, flatten_ids, offsets, backgrounds, width, height, visibility_min_T=0.5,
-              count_touched=True, n_touched=None):
-    """-> render [C,H,W,5], alphas [C,H,W,1], n_touched int64 [C,N] (n_touched: optional pre-zeroed buffer)."""
+              count_touched=True, n_touched=None, det=None, radii=None, isect_ids=None):
+    """-> render [C,H,W,5], alphas [C,H,W,1], n_touched int64 [C,N] (n_touched: optional pre-zeroed buffer).
+    det (None: the module default): deterministic backward; it needs radii [C,N] and the sorted isect_ids."""
     tile_w, tile_h = math.ceil(width / TILE), math.ceil(height / TILE)
+    det = deterministic if det is None else bool(det)
     return _Composite.apply(rec, means2d, flatten_ids, offsets, backgrounds, int(width), int(height),
-                            tile_w, tile_h, float(visibility_min_T), bool(count_touched), n_touched)
+                            tile_w, tile_h, float(visibility_min_T), bool(count_touched), n_touched,
+                            det, radii if det else None, isect_ids if det else None)
 
 
 @torch.no_grad()

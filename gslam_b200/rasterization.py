@@ -94,6 +94,7 @@ def rasterization(
     visibility_min_T: float = 0.5,
     mask: Optional[Tensor] = None,
     sh_degree: Optional[int] = None,
+    deterministic: Optional[bool] = None,
 ) -> RasterizationOutput:
     """Rasterize N Gaussians to C image planes; see the reference docstring
     (gslam/rasterization.py:72-119) for the argument meanings.
@@ -102,7 +103,10 @@ def rasterization(
     cfg4): None keeps the reference's ``sigmoid(logit_colors)``; 0..3 reads ``logit_colors`` as real
     spherical-harmonics coefficients ``[N, K >= (sh_degree+1)^2, 3]`` and colours each (view,
     Gaussian) pair ``max(SH(normalize(mean - camera centre)) + 0.5, 0)``, gradients to the
-    coefficients and to the means."""
+    coefficients and to the means.
+
+    ``deterministic`` (None: ``ops.deterministic``): the backward pass accumulates in a fixed order
+    instead of with float atomics, so gradients are bit-identical from run to run (include/gsb.h)."""
     N = means.shape[0]
     C = viewmats.shape[0]
     assert means.shape == (N, 3), means.shape
@@ -138,7 +142,7 @@ def rasterization(
     radii, means2d, rec, tiles_per_gauss, tile_counts = ops.project(
         means, quats, log_scales, logit_opacities, logit_colors, log_uncertainties, viewmats, Ks,
         width, height, eps2d, near_plane, far_plane, radius_clip, tile_counts=zeros.tile_counts,
-        sh_degree=sh_degree)
+        sh_degree=sh_degree, det=deterministic)
 
     # K4+K5: counting sort by tile + per-tile depth sort (bit-identical to the upstream
     # emit / stable radix sort / offset-encode chain, which ops.isect_tiles still provides)
@@ -155,7 +159,8 @@ def rasterization(
 
     # K6
     render, alphas, n_touched = ops.composite(rec, means2d, flatten_ids, offsets, bg5, width,
-                                              height, visibility_min_T, n_touched=zeros.n_touched)
+                                              height, visibility_min_T, n_touched=zeros.n_touched,
+                                              det=deterministic, radii=radii, isect_ids=isect_ids)
 
     out = RasterizationOutput(
         rgbs=render[..., :3] if render_mode not in ("D",) else None,

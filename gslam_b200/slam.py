@@ -76,6 +76,9 @@ class MapConfig:
     graph_min_iters: int = 10
     graph_check_every: int = 5
     optimize_poses: bool = True             # optimize_poses_lbfgs after every idle mapping round (:851)
+    deterministic: bool = False             # fixed-order gradient accumulation in mapping AND tracking
+                                            # (ops.deterministic): the same sequence gives the same keyframes,
+                                            # map and trajectory, bit for bit, from run to run
 
 
 @dataclass
@@ -140,6 +143,7 @@ class Slam:
         self.gen = torch.Generator(device=self.dev).manual_seed(seed)
         track_conf = track_conf or TrackingConfig()
         track_conf.use_gt_depths = self.conf.use_gt_depths
+        track_conf.deterministic = track_conf.deterministic or self.conf.deterministic
         self.tracker = Tracker(self.camera, track_conf, device)
         c = self.conf
         self.insertion = InsertFromDepthMap(0.1 * c.initial_scale, 0.2 * c.initial_scale, 0.1,
@@ -501,6 +505,11 @@ class Slam:
     def process_frame(self, img: Tensor, idle_rounds: int = 1, gt_depth: Optional[Tensor] = None) -> Tensor:
         """Track `img` [H,W,3] (device, values in [0,1]) and let the backend work; returns the frame's
         world->camera matrix."""
+        from . import ops
+        with ops.deterministic_mode(self.conf.deterministic):
+            return self._process_frame(img, idle_rounds, gt_depth)
+
+    def _process_frame(self, img: Tensor, idle_rounds: int, gt_depth: Optional[Tensor]) -> Tensor:
         idx = self.stats.frames
         sync = torch.cuda.synchronize
         if idx == 0:

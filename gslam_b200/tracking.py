@@ -39,6 +39,7 @@ from typing import List, Optional
 import torch
 from torch import Tensor
 
+from . import ops
 from .graph import GraphedStep
 from .lbfgs import lbfgs_minimize
 from .losses import tracking_loss
@@ -63,6 +64,8 @@ class TrackingConfig:
     lbfgs_max_iter: int = 20                   # torch.optim.LBFGS default (max_eval = 25); 0 skips the phase
     lbfgs_tolerance_change: float = 1e-9
     exposure_lr: float = 0.01                  # SGD param-group lr of the exposure (:204-209)
+    deterministic: bool = False                # fixed-order gradient accumulation (ops.deterministic): the same
+                                               # frame gives bit-identical poses from run to run
 
 
 class StopOnPlateau:
@@ -253,7 +256,8 @@ class Tracker:
             fn = {"closure": self._step_closure, "adam": self._step_adam, "sgd": self._step_sgd}[kind]
             saved = [t.clone() for t in (self.theta.detach(), self.m, self.v, self.step_no, self.lr_scale,
                                          self.ring_pos)]
-            g = GraphedStep(fn, headroom=self.headroom)
+            with ops.deterministic_mode(self.conf.deterministic):     # baked into the captured kernels
+                g = GraphedStep(fn, headroom=self.headroom)
             self.n_captures += 1
             # the eager warm-up runs of the capture moved the unknowns; put them back
             with torch.no_grad():

@@ -72,7 +72,11 @@ int gsb_project_fwd(const float* means, const float* quats, const float* log_sca
  * v_log_scales[N,3] v_logit_opacities[N] v_logit_colors[N,3] v_log_unc[N]
  * (any may be NULL when need_gauss_grads == 0) and v_viewmats[C,4,4] (must be
  * zeroed by the caller; accumulated atomically; may be NULL).  With SH colours pass
- * logit_colors = v_logit_colors = NULL and call gsb_sh_bwd afterwards. */
+ * logit_colors = v_logit_colors = NULL and call gsb_sh_bwd afterwards.
+ * Deterministic mode: det_partials (NULL = atomics) is scratch of gsb_project_bwd_det_floats(C, N)
+ * floats; the per-block pose-gradient sums go there and are added in a fixed order, so v_viewmats is
+ * bit-identical from run to run. */
+size_t gsb_project_bwd_det_floats(int C, int N);
 int gsb_project_bwd(const float* means, const float* quats, const float* log_scales,
                     const float* logit_opacities, const float* logit_colors,
                     const float* log_unc, const float* viewmats, const float* Ks,
@@ -82,7 +86,7 @@ int gsb_project_bwd(const float* means, const float* quats, const float* log_sca
                     int need_gauss_grads,
                     float* v_means, float* v_quats, float* v_log_scales,
                     float* v_logit_opacities, float* v_logit_colors, float* v_log_unc,
-                    float* v_viewmats, void* stream);
+                    float* v_viewmats, float* det_partials, void* stream);
 
 /* Backward of the SH colours of gsb_project_fwd: v_sh[N, sh_stride, 3] is overwritten (summed over
  * cameras), the view-direction term is ADDED to v_means[N,3] (may be NULL), so call it after
@@ -161,12 +165,23 @@ int gsb_composite_fwd(const float* rec, const int32_t* flatten_ids, const int32_
                       int64_t* pair_count, void* stream);
 
 /* K7: compositing backward.  v_rec[C,N,12] must be zeroed by the caller and is
- * accumulated atomically (x,y slots hold v_means2d).  v_backgrounds[C,5] may be NULL. */
+ * accumulated atomically (x,y slots hold v_means2d).  v_backgrounds[C,5] may be NULL.
+ * Deterministic mode (det_workspace != NULL, 16-byte aligned, gsb_composite_bwd_det_bytes(capacity)
+ * bytes, capacity = n_isects or, for n_isects < 0, -n_isects - 1 > 0): every (tile unit, list entry)
+ * gradient row is stored instead of added atomically, and a second kernel sums each Gaussian's rows
+ * in a fixed order (tiles row-major, units in order), finding the entry in each tile's sorted list
+ * by its depth bits in isect_ids[capacity] (the low word) and its flatten id.  v_rec is then
+ * overwritten (no zeroing needed) and bit-identical from run to run; radii[C,N] and isect_ids are
+ * required, v_backgrounds must be NULL (it is sum_pixels (1 - alpha) v_render, a plain reduction
+ * the caller can do in any deterministic way). */
+size_t gsb_composite_bwd_det_bytes(int64_t capacity);
 int gsb_composite_bwd(const float* rec, const int32_t* flatten_ids, const int32_t* offsets,
                       const float* backgrounds, int C, int N, int width, int height,
                       int tile_w, int tile_h, int64_t n_isects, const float* render_alphas,
                       const int32_t* last_ids, const float* v_render, const float* v_alphas,
-                      float* v_rec, float* v_backgrounds, void* stream);
+                      float* v_rec, float* v_backgrounds, const int32_t* radii,
+                      const int64_t* isect_ids, void* det_workspace, size_t det_workspace_bytes,
+                      void* stream);
 
 /* K9: fused_ssim (reference gslam/backend.py:303-307; rahul-goel/fused-ssim@30fb258).
  * img1/img2 are [N,C,H,W] addressed through element strides (host arrays of 4: n, c, h, w),
@@ -176,9 +191,14 @@ int gsb_composite_bwd(const float* rec, const int32_t* flatten_ids, const int32_
  * backward pass needs.  gsb_ssim_bwd writes (accumulate == 0) or adds (!= 0)
  *   (*grad) * coef * d(ssim_sum)/d(img1)   into v_img1 (element strides strides_out_host);
  * grad is a DEVICE scalar (NULL = 1) so the upstream gradient needs no host sync. */
+/* Deterministic mode: det_partials (NULL = one float atomic per CTA) is scratch of
+ * gsb_ssim_fwd_det_floats(N, C, H, W) floats; the CTA sums are added in a fixed order and ssim_sum is
+ * overwritten. */
+size_t gsb_ssim_fwd_det_floats(int N, int C, int H, int W);
 int gsb_ssim_fwd(const float* img1, const float* img2, const int64_t* strides1_host,
                  const int64_t* strides2_host, int N, int C, int H, int W, int valid,
-                 float* ssim_sum, float* dm_dmu1, float* dm_ds1, float* dm_ds12, void* stream);
+                 float* ssim_sum, float* dm_dmu1, float* dm_ds1, float* dm_ds12,
+                 float* det_partials, void* stream);
 int gsb_ssim_bwd(const float* img1, const float* img2, const int64_t* strides1_host,
                  const int64_t* strides2_host, int N, int C, int H, int W, const float* dm_dmu1,
                  const float* dm_ds1, const float* dm_ds12, const float* grad, float coef,
@@ -192,10 +212,14 @@ int gsb_ssim_bwd(const float* img1, const float* img2, const int64_t* strides1_h
  * loss_sum[3] (zeroed by the caller) receives the two un-normalised sums (+ a block ticket);
  * loss_out[2] (may be NULL) receives (coef * loss, loss), written by the last block; v_render[C,H,W,5]
  * is overwritten with coef * dLoss/drender; v_exposure[C,2] (zeroed; may be NULL) accumulates
- * coef * dLoss/dexposure. */
+ * coef * dLoss/dexposure.
+ * Deterministic mode: det_partials (NULL = float atomics) is scratch of
+ * gsb_photo_loss_det_floats(C, H, W) floats; the CTA sums are added in a fixed order by a second
+ * launch that overwrites loss_sum[0..1], loss_out and v_exposure. */
+size_t gsb_photo_loss_det_floats(int C, int H, int W);
 int gsb_photo_loss(const float* render, const float* gt, const float* exposure, int mode, int C,
                    int H, int W, float coef, float* loss_sum, float* loss_out, float* v_render,
-                   float* v_exposure, void* stream);
+                   float* v_exposure, float* det_partials, void* stream);
 int gsb_scale_by_scalar(float* x, int64_t n, const float* grad, void* stream);
 
 /* K12/K13: ONE launch of Adam over up to 8 tensors (reference gslam/backend.py:559-602 steps
@@ -220,10 +244,11 @@ int gsb_adam_multi(const gsb_adam_tensor* tensors_host, int n_tensors, float bet
  * gsb_vis_count: vis_count[n] = #views with radii[c,n] > 0 (gslam/backend.py:287, :357).
  * gsb_isotropic_reg: the isotropic regulariser of gslam/backend.py:288-296 on the Gaussians with
  * vis_count > 0: adds weight * d/ds sum|exp(s) - exp(mean s).detach()| to v_log_scales[N,3] and the
- * unweighted sum to *loss_sum (float, may be NULL, accumulated atomically). */
+ * unweighted sum to *loss_sum (float, may be NULL, accumulated atomically; with det_partials, scratch
+ * of ceil(N / 256) floats, the CTA sums are added in a fixed order and *loss_sum is overwritten). */
 int gsb_vis_count(const int32_t* radii, int C, int64_t N, int32_t* vis_count, void* stream);
 int gsb_isotropic_reg(const float* log_scales, const int32_t* vis_count, int64_t N, float weight,
-                      float* v_log_scales, float* loss_sum, void* stream);
+                      float* v_log_scales, float* loss_sum, float* det_partials, void* stream);
 
 /* ---- densify / prune surgery ------------------------------------------------
  * Replaces the per-tensor `value[keep_mask]` / `torch.cat` loops of gslam/pruning.py:10-53 and

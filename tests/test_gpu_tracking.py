@@ -107,26 +107,31 @@ def test_lbfgs_tracking_recovers_the_pose_like_the_reference_loop(cuda):
     tr.set_map(splats)
     r = tr.track_lbfgs(gt, torch.eye(4, device=cuda))
     start = _pose_error(torch.eye(4, device=cuda), true)
+    err, err_ref = _pose_error(r.viewmat, true), _pose_error(pose().detach(), true)
     assert r.loss < 0.5 * loss0, (r.loss, loss0)
-    # same algorithm, but the gradient's atomics reorder and the line search amplifies it: close, not equal
+    # Same algorithm and schedule as the torch loop above; the claim is relative to THAT loop run on the
+    # same problem (what the schedule -- lr 0.002, 10 Adam + <= 25 L-BFGS evaluations, free exposure --
+    # can recover is a property of the problem, not of the tracker): float64 host L-BFGS vs torch's
+    # float32 one and reordered atomics perturb the line search, so close, not equal.
     assert r.loss <= 1.5 * last[0] + 1e-7, (r.loss, last[0])
-    assert _pose_error(r.viewmat, true) < 0.5 * start
-    assert _pose_error(r.viewmat, true) <= 2.0 * _pose_error(pose().detach(), true) + 1e-3
+    assert err < start, (err, err_ref, start)
+    assert err <= 1.5 * err_ref + 1e-3, (err, err_ref, start)
     # one sync per L-BFGS evaluation, none in the Adam phase
     assert r.n_syncs <= r.n_evals - 10 + 1
 
 
 def test_graphs_are_captured_once_per_map_and_reused_across_frames(cuda):
     splats, cam, gt, true = _problem(cuda, n=8_000)
-    tr = Tracker(cam, TrackingConfig(), cuda)
+    tr = Tracker(cam, TrackingConfig(deterministic=True), cuda)
     tr.set_map(splats)
     a = tr.track_lbfgs(gt, torch.eye(4, device=cuda))
     graphs = dict(tr._graphs)
     b = tr.track_lbfgs(gt.flip(1), a.viewmat)           # another image, another start
     assert all(tr._graphs[k] is g for k, g in graphs.items()) and len(tr._graphs) == 2
     c = tr.track_lbfgs(gt, torch.eye(4, device=cuda))   # the first problem again: same answer
-    # not bitwise: the gradient's atomics reorder between replays and the line search amplifies it
-    assert torch.allclose(a.viewmat, c.viewmat, atol=5e-3) and abs(a.loss - c.loss) < 0.3 * a.loss
+    # bitwise, because the tracker runs in deterministic mode (with atomics the gradient's last bits
+    # change between replays and the line search amplifies that into another path)
+    assert torch.equal(a.viewmat, c.viewmat) and a.loss == c.loss
     assert torch.isfinite(b.viewmat).all()
     # a sync with a map that fits the capacity keeps the graphs; dead rows render nothing
     assert tr.capacity >= 8_000 and tr.n_live == 8_000
