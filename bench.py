@@ -51,7 +51,20 @@ def parse():
     ap.add_argument("--track-frames", type=int, default=12)
     ap.add_argument("--slam-frames", type=int, default=60)
     ap.add_argument("--no-sequence", action="store_true")
+    ap.add_argument("--no-f64", action="store_true", help="skip the float64 oracle run of the parity report")
+    ap.add_argument("--no-cfg1", action="store_true", help="skip the 10k-Gaussian 320x240 leg (BASELINE configs[0])")
     return ap.parse_args()
+
+
+def csrc_sha() -> str:
+    """Hash of the kernel sources (gslam_b200/csrc/*, include/gsb.h): what a profile belongs to."""
+    import hashlib
+    h = hashlib.sha256()
+    d = os.path.join(ROOT, "gslam_b200", "csrc")
+    for fn in sorted(os.listdir(d)) + ["../../include/gsb.h"]:
+        with open(os.path.join(d, fn), "rb") as f:
+            h.update(fn.encode() + b"\0" + f.read())
+    return h.hexdigest()[:12]
 
 
 def peaks():
@@ -63,59 +76,117 @@ def peaks():
 
 
 # ----------------------------------------------------------------------------------------------
-# CPU arm: the oracle on a bounded sample (a band of tile rows of the same 640x480 view)
+# CPU arm: the oracle (oracle/torch_ref.py) on the SAME full view as the GPU arm, on the host cores
 # ----------------------------------------------------------------------------------------------
-def cpu_oracle_rate(n_gauss: int, band_rows: int, reps: int = 1, warm: int = 0):
-    """it/s of the CPU oracle, scaled from a band of `band_rows` tile rows (of 30) to the full view."""
+def workload_string(n: int, world: int = 1, scale: float = 1.0) -> str:
+    w, h = int(round(640 * scale)), int(round(480 * scale))
+    return (f"cfg2-shape: 1 view per GPU, N={n}, {w}x{h} TUM-fr1, RGB+D+beta, "
+            "fwd + active-NeRF loss + bwd (all Gaussian grads + viewmat grad)"
+            + (", independent replicas (tracking does not shard)" if world > 1 else ""))
+
+
+def cpu_oracle_step(sc, gt, dtype=None, stats: bool = False):
+    """One fwd + active-NeRF tracking loss + bwd of the CPU oracle on the whole view ->
+    (seconds, dict of outputs and gradients)."""
+    import torch
+    from oracle import torch_ref as R
+    cast = (lambda t: t.to(dtype)) if dtype is not None else (lambda t: t)
+    ps = [cast(p.clone()).requires_grad_(True) for p in sc.params()]
+    vm = cast(sc.viewmats.clone()).requires_grad_(True)
+    K, g = cast(sc.Ks), cast(gt)
+    t0 = time.perf_counter()
+    res = R.rasterization(ps[0], ps[1], ps[2], ps[3], ps[4], vm, K, sc.width, sc.height,
+                          backgrounds=torch.zeros(1, 3, dtype=vm.dtype), render_mode="RGB+D",
+                          log_uncertainties=ps[5], return_stats=stats)
+    out, st = res if stats else (res, None)
+    loss = R.tracking_loss(g, out.rgbs, out.betas)
+    loss.backward()
+    dt = time.perf_counter() - t0
+    names = ["g_means", "g_quats", "g_log_scales", "g_logit_opacities", "g_logit_colors", "g_log_unc"]
+    d = {"rgb": out.rgbs.detach(), "depth": out.depthmaps.detach(), "beta": out.betas.detach(),
+         "alpha": out.alphas.detach(), "loss": loss.detach(), "g_viewmat": vm.grad[:, :3],
+         "n_isects": int(out.flatten_ids.numel()), "pairs": st["P"] if st else None,
+         "n_touched": out.n_touched, "radii": out.radii}
+    d.update({nm: p.grad for nm, p in zip(names, ps)})
+    return dt, d
+
+
+def cpu_oracle_rate(n_gauss: int, reps: int = 1, warm: int = 0, scale: float = 1.0, keep: bool = False):
+    """it/s of the CPU oracle on the FULL view (every step is the whole workload, nothing is scaled):
+    -> (it/s, median seconds per step, cores, sample description, outputs of the last step or None)."""
     import torch
     from gslam_b200.synthetic import make_scene, target_images
-    from oracle import torch_ref as R
 
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
-    sc = make_scene(n_gauss, 1, "tum", 1.0)
-    total_rows = (sc.height + 15) // 16
-    band_rows = max(1, min(band_rows, total_rows))
-    h = min(band_rows * 16, sc.height)
-    gt = target_images(1, sc.height, sc.width)[:, :h]
-    times = []
+    sc = make_scene(n_gauss, 1, "tum", scale)
+    gt = target_images(1, sc.height, sc.width)
+    times, last = [], None
     for it in range(warm + reps):
-        ps = [p.clone().requires_grad_(True) for p in sc.params()]
-        vm = sc.viewmats.clone().requires_grad_(True)
-        t0 = time.perf_counter()
-        out = R.rasterization(ps[0], ps[1], ps[2], ps[3], ps[4], vm, sc.Ks, sc.width, h,
-                              backgrounds=torch.zeros(1, 3), render_mode="RGB+D", log_uncertainties=ps[5])
-        loss = R.tracking_loss(gt, out.rgbs, out.betas)
-        loss.backward()
-        dt = time.perf_counter() - t0
+        dt, d = cpu_oracle_step(sc, gt, stats=keep and it == warm + reps - 1)
         if it >= warm:
             times.append(dt)
-    frac = h / sc.height
+        last = d if keep else None
     t = statistics.median(times)
-    sample = (f"oracle/torch_ref.py fwd+loss+bwd on {n_gauss} Gaussians, rows 0..{h} of the 640x480 view "
-              f"({band_rows}/{total_rows} tile rows), time scaled by {1 / frac:.2f} to a full view")
-    return frac / t, t, cores, sample
+    sample = (f"oracle/torch_ref.py fwd+loss+bwd on {n_gauss} Gaussians, the whole {sc.width}x{sc.height} view, "
+              f"{reps} timed step(s) after {warm} warm-up, median; nothing scaled")
+    return 1.0 / t, t, cores, sample, last
 
 
 def run_reference(args):
+    """The reference arm of this tier: the CPU oracle port on the host cores, the SAME workload as the
+    GPU arm (whole 640x480 view, 200k Gaussians), exactly `warmup` untimed + `steps` timed steps."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    k = args.steps + args.warmup
-    # ~23 s per full view on 8 cores; keep the whole run near 2-3 minutes
-    band = max(1, min(30, int(30 * 150.0 / (23.0 * max(k, 1)))))
-    value, t, cores, sample = cpu_oracle_rate(args.n_gauss, band, reps=args.steps, warm=args.warmup)
+    t0 = time.perf_counter()
+    value, t, cores, sample, _ = cpu_oracle_rate(args.n_gauss, reps=args.steps, warm=args.warmup)
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 / value,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic",
-        "config": {"workload": f"cfg2-shape: 1 view, N={args.n_gauss}, 640x480, RGB+D+beta, fwd+bwd",
-                   "note": "CPU oracle (port of the reference math); reference kernels are un-vendored CUDA"},
+        "config": {"workload": workload_string(args.n_gauss, 1),
+                   "note": "CPU oracle (port of the reference math); reference kernels are un-vendored CUDA",
+                   "extrapolated": False, "wall_s": None},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
+    line["config"]["wall_s"] = round(time.perf_counter() - t0, 1)
     print(json.dumps(line), flush=True)
+
+
+def rel_err(a, b) -> float:
+    """||a - b|| / ||b|| in float64 on the host."""
+    a, b = a.detach().double().cpu(), b.detach().double().cpu()
+    return float((a - b).norm() / b.norm().clamp(min=1e-30))
+
+
+PARITY_KEYS = ["rgb", "depth", "beta", "alpha", "g_means", "g_quats", "g_log_scales", "g_logit_opacities",
+               "g_logit_colors", "g_log_unc", "g_viewmat"]
+IMG_TOL, GRAD_TOL = 1e-4, 1e-3          # BASELINE.json north_star tolerances
+
+
+def parity_report(gpu: dict, ref: dict, ref64: dict = None) -> dict:
+    """Relative errors of the GPU step against the oracle's on the identical inputs; with the float64
+    oracle also each side's error against it (so "GPU fp32 error <= oracle fp32 error" can be read off)."""
+    rep = {k: rel_err(gpu[k], ref[k]) for k in PARITY_KEYS}
+    rep["loss"] = abs(float(gpu["loss"]) - float(ref["loss"])) / max(abs(float(ref["loss"])), 1e-30)
+    rep["n_isects_equal"] = gpu["n_isects"] == ref["n_isects"]
+    rep["pairs_equal"] = None if ref.get("pairs") is None or gpu.get("pairs") is None else gpu["pairs"] == ref["pairs"]
+    rep["n_isects"] = [gpu["n_isects"], ref["n_isects"]]
+    rep["pairs"] = [gpu.get("pairs"), ref.get("pairs")]
+    nt_g, nt_r = gpu["n_touched"].cpu().long(), ref["n_touched"].long()
+    rep["n_touched_mismatch_frac"] = float((nt_g != nt_r).float().mean())
+    rep["radii_mismatch_frac"] = float((gpu["radii"].cpu() != ref["radii"]).float().mean())
+    if ref64 is not None:
+        rep["vs_f64"] = {k: {"gpu_f32": rel_err(gpu[k], ref64[k]), "oracle_f32": rel_err(ref[k], ref64[k])}
+                         for k in PARITY_KEYS}
+    worst_img = max(rep[k] for k in PARITY_KEYS[:4])
+    worst_grad = max(rep[k] for k in PARITY_KEYS[4:])
+    rep["tolerance"] = {"images": IMG_TOL, "gradients": GRAD_TOL}
+    rep["ok"] = bool(worst_img <= IMG_TOL and worst_grad <= GRAD_TOL)
+    return rep
 
 
 # ----------------------------------------------------------------------------------------------
@@ -364,12 +435,77 @@ def slam_sequence_leg(args, dev, rgbd: bool):
             "includes": "frame 0 initialisation (up to 400 mapping iterations)"}
 
 
+def cfg1_leg(dev):
+    """BASELINE.json configs[0]: the CPU oracle's own case -- 10k Gaussians, 320x240, one view, fwd + loss +
+    bwd -- timed on the host cores (median of 5 after 1 warm-up) with the GPU path beside it at the same
+    shape (CUDA-graph replay, L2 flushed between steps), and the parity of the two."""
+    import torch
+    from gslam_b200.graph import GraphedStep
+    from gslam_b200.losses import tracking_loss
+    from gslam_b200.rasterization import rasterization
+    from gslam_b200.synthetic import make_scene, target_images
+    n, scale = 10_000, 0.5
+    v, tsec, cores, sample, ref = cpu_oracle_rate(n, reps=5, warm=1, scale=scale, keep=True)
+    sc = make_scene(n, 1, "tum", scale)
+    g = sc.to(dev)
+    params = [p.clone().requires_grad_(True) for p in g.params()]
+    vm = g.viewmats.clone().requires_grad_(True)
+    gt = target_images(1, sc.height, sc.width).to(dev)
+    bg = torch.zeros(1, 3, device=dev)
+    box = {}
+
+    def step():
+        for p in params:
+            p.grad = None
+        vm.grad = None
+        out = rasterization(params[0], params[1], params[2], params[3], params[4], vm, g.Ks, sc.width, sc.height,
+                            packed=False, render_mode="RGB+D", log_uncertainties=params[5], backgrounds=bg)
+        loss = tracking_loss(out.render, gt, None, "active-nerf", unit_upstream=True)
+        loss.backward()
+        if box.get("keep"):
+            box["out"] = out
+        return loss
+
+    box["keep"] = True
+    loss = step()
+    out = box.pop("out")
+    box["keep"] = False
+    names = ["g_means", "g_quats", "g_log_scales", "g_logit_opacities", "g_logit_colors", "g_log_unc"]
+    gpu = {"rgb": out.rgbs.detach().cpu(), "depth": out.depthmaps.detach().cpu(), "beta": out.betas.detach().cpu(),
+           "alpha": out.alphas.detach().cpu(), "loss": loss.detach().cpu(), "g_viewmat": vm.grad[:, :3].cpu(),
+           "n_isects": int(out.flatten_ids.numel()), "pairs": None, "n_touched": out.n_touched.cpu(),
+           "radii": out.radii.cpu()}
+    gpu.update({nm: p.grad.cpu() for nm, p in zip(names, params)})
+    # nothing of the eager step may stay alive into the capture: a live output keeps the parameters'
+    # AccumulateGrad nodes, and the stream they ran on, in the graph (cudaErrorStreamCaptureImplicit)
+    del out, loss
+    gs = GraphedStep(step)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    steps = 30
+    for _ in range(5):
+        gs.replay()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+    for e0, e1 in ev:
+        flush.zero_()
+        e0.record()
+        gs.replay()
+        e1.record()
+    torch.cuda.synchronize()
+    gs.check()
+    ms = sum(a.elapsed_time(b) for a, b in ev) / steps
+    return {"workload": workload_string(n, 1, scale) + " (BASELINE.json configs[0])",
+            "cpu_oracle": {"value": v, "unit": UNIT, "cores": cores, "seconds": tsec, "sample": sample},
+            "gpu": {"value": 1e3 / ms, "unit": UNIT, "ms_per_step": ms, "steps": steps,
+                    "timed_loop": "CUDA-graph replay, L2 flushed between steps"},
+            "parity": parity_report(gpu, ref)}
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
     from gslam_b200 import _lib, ops
     from gslam_b200.rasterization import rasterization
-    from gslam_b200.synthetic import make_scene, target_images
+    from gslam_b200.synthetic import make_scene, target_images  # noqa: F811
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -468,11 +604,20 @@ def run_ours(args):
 
     # ---- per-kernel durations (CUDA events around each C-ABI call, same steps, live) -------------
     ops.pair_counter = torch.zeros(1, dtype=torch.int64, device=dev)
-    _, out = step(params, vm, K, gt)
+    loss_g, out = step(params, vm, K, gt)
     torch.cuda.synchronize()
     P = int(ops.pair_counter.item())
     I = int(out.isect_ids.numel())
     ops.pair_counter = None
+    # what the parity report compares with the oracle's step on the identical inputs (cpu_baseline leg)
+    gpu_step = None
+    if world == 1 and not args.no_cpu_baseline:
+        gnames = ["g_means", "g_quats", "g_log_scales", "g_logit_opacities", "g_logit_colors", "g_log_unc"]
+        gpu_step = {"rgb": out.rgbs.detach().cpu(), "depth": out.depthmaps.detach().cpu(),
+                    "beta": out.betas.detach().cpu(), "alpha": out.alphas.detach().cpu(),
+                    "loss": loss_g.detach().cpu(), "g_viewmat": vm.grad[:, :3].cpu(), "n_isects": I, "pairs": P,
+                    "n_touched": out.n_touched.cpu(), "radii": out.radii.cpu()}
+        gpu_step.update({nm: p.grad.cpu() for nm, p in zip(gnames, params)})
     del out
     # per-kernel pass: an event pair around every C-ABI call of live steps.  The host must run AHEAD of
     # the device for such a pair to bracket the kernel alone -- otherwise it also spans the launch
@@ -612,11 +757,19 @@ def run_ours(args):
             "gsb_scale_by_scalar": 40 * px,
         }
         # DRAM bytes per launch from the committed `ncu --set full` capture (tools/ncu_traffic.py)
-        traffic = {}
-        tpath = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "traffic.json")
+        # (tools/ncu_traffic.py stamps the file with the hash of the kernel sources it was captured from;
+        # a capture of other sources is refused rather than quoted)
+        traffic, traffic_note = {}, None
+        tpath = os.path.join(ROOT, "profiles", "traffic.json")
         if os.path.exists(tpath) and n == 200_000:
             with open(tpath) as f:
-                traffic = json.load(f).get("dram_bytes_per_launch", {})
+                tj = json.load(f)
+            if tj.get("csrc_sha") == csrc_sha():
+                traffic = tj.get("dram_bytes_per_launch", {})
+                traffic_note = f"ncu --set full capture of csrc {tj.get('csrc_sha')} ({tj.get('captured', '?')})"
+            else:
+                traffic_note = (f"profiles/traffic.json is of csrc {tj.get('csrc_sha')}, this tree is {csrc_sha()}: "
+                                "stale capture refused, traffic = null")
         stages = []
         for name, (calls, msk) in sorted(kt.items(), key=lambda kv: -kv[1][1]):
             if name not in alg:
@@ -625,30 +778,40 @@ def run_ours(args):
             stages.append({"kernel": name, "ms": round(msk, 5), "bound": "hbm", "achieved": round(ach, 2),
                            "peak": hbm, "unit": "GB/s", "frac": round(ach / hbm, 5),
                            "algorithmic_bytes": alg[name], "traffic": traffic.get(name)})
-        # FP32 view of the compositing kernels: pairs evaluated x FMA-class instructions per pair
-        fp32_peak = 148 * 128 * sm_max * 1e6          # FMA lanes/s
+        # What bounds each stage.  The compositing kernels walk P (pixel, Gaussian) pairs out of
+        # L2-resident lists (DRAM traffic is a tenth of their algorithmic bytes): their roofline is the
+        # FP32 lanes, 148 SM x 128 lanes x 2 flop x f_SM, against the oracle-defined pair count P times
+        # the flops per pair of SURVEY 8d; the HBM fraction stays beside it as `hbm_frac`.  The one-CTA
+        # tile scan is a latency chain (its bytes are nothing).
+        fp32_peak_tflops = 148 * 128 * 2 * sm_max * 1e6 / 1e12
+        flop_per_pair = {"gsb_composite_fwd": 2 * (9 + 5) + 1, "gsb_composite_bwd": 45 + 3 * 5 + 1}
         for st in stages:
-            if st["kernel"] == "gsb_composite_fwd":
-                st["fp32"] = {"pairs": P, "flop_per_pair": 2 * (9 + 5) + 1,
-                              "achieved_gpairs_s": round(P / (st["ms"] * 1e-3) / 1e9, 3),
-                              "fma_frac": round(P * (9 + 5) / (st["ms"] * 1e-3) / fp32_peak, 5)}
-            if st["kernel"] == "gsb_composite_bwd":
-                st["fp32"] = {"pairs": P, "flop_per_pair": 45 + 3 * 5 + 1,
-                              "achieved_gpairs_s": round(P / (st["ms"] * 1e-3) / 1e9, 3),
-                              "fma_frac": round(P * 30 / (st["ms"] * 1e-3) / fp32_peak, 5)}
+            if st["kernel"] in flop_per_pair:
+                fpp = flop_per_pair[st["kernel"]]
+                tfl = P * fpp / (st["ms"] * 1e-3) / 1e12
+                st.update({"bound": "fp32", "hbm_frac": st["frac"], "hbm_achieved_gbs": st["achieved"],
+                           "achieved": round(tfl, 3), "peak": round(fp32_peak_tflops, 2), "unit": "TFLOP/s",
+                           "frac": round(tfl / fp32_peak_tflops, 5), "pairs": P, "flop_per_pair": fpp,
+                           "achieved_gpairs_s": round(P / (st["ms"] * 1e-3) / 1e9, 3),
+                           "peak_how": f"148 SM x 128 FP32 lanes x 2 flop x {sm_max:.0f} MHz (nominal; no measured "
+                                       "FP32 figure in MEASURED_PEAKS.json)"})
+            elif st["kernel"] == "gsb_tile_scan":
+                st.update({"bound": "latency", "note": "one CTA, serial scan of C*T counters"})
         dom = stages[0] if stages else None
         roofline = None
         if dom:
-            roofline = {"kernel": dom["kernel"], "bound": "hbm", "achieved": dom["achieved"], "peak": hbm,
-                        "unit": "GB/s", "frac": dom["frac"], "traffic": dom["traffic"], "peak_source": which,
+            roofline = {"kernel": dom["kernel"], "bound": dom["bound"], "achieved": dom["achieved"],
+                        "peak": dom["peak"], "unit": dom["unit"], "frac": dom["frac"], "traffic": dom["traffic"],
+                        "peak_source": which if dom["bound"] == "hbm" else "nominal FP32 lanes",
                         "ms_per_launch": dom["ms"]}
+            for k in ("hbm_frac", "pairs", "flop_per_pair", "algorithmic_bytes"):
+                if k in dom:
+                    roofline[k] = dom[k]
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": f"cfg2-shape: 1 view per GPU, N={n}, 640x480 TUM-fr1, RGB+D+beta, "
-                                   "fwd + active-NeRF loss + bwd (all Gaussian grads + viewmat grad)"
-                                   + (", independent replicas (tracking does not shard)" if world > 1 else ""),
+            "config": {"workload": workload_string(n, world),
                        "l2": "256 MiB memset between timed steps, outside each step's event pair",
                        "n_isects": I, "pairs": P},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
@@ -662,17 +825,41 @@ def run_ours(args):
             "wall_s_timed_region": wall,
             "clocks": clocks,
             "roofline": roofline,
+            "traffic_source": traffic_note,
             "roofline_stages": stages,
             "mapping": mapping,
             "tracking_closure": closure,
             "tracking_frames": track_frames,
             "sequence": slam_seq,
         }
+        parity_ok = True
         if world == 1 and not args.no_cpu_baseline:
-            v, tsec, cores, sample = cpu_oracle_rate(n, band_rows=30, reps=1)
+            # the oracle's step on the identical inputs: timed (cpu_baseline) AND compared (parity)
+            v, tsec, cores, sample, ref = cpu_oracle_rate(n, reps=1, keep=True)
             line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
                                     "sample": sample, "seconds": tsec}
+            ref64 = None
+            if not args.no_f64:
+                _, ref64 = cpu_oracle_step(make_scene(n, 1, "tum", 1.0), target_images(1, H, W), torch.float64)
+            line["parity"] = parity_report(gpu_step, ref, ref64)
+            line["parity"]["what"] = (f"GPU step vs oracle/torch_ref.py on the identical {n}-Gaussian 640x480 view "
+                                      "(relative L2 errors; images <= 1e-4, gradients <= 1e-3)")
+            parity_ok = line["parity"]["ok"]
+            if not args.no_cfg1:
+                try:
+                    line["cfg1"] = cfg1_leg(dev)
+                    parity_ok = parity_ok and line["cfg1"]["parity"]["ok"]
+                except Exception as e:   # noqa: BLE001  (a secondary leg must not take the headline line down)
+                    line["cfg1"] = {"error": f"{type(e).__name__}: {e}",
+                                    "where": traceback.format_exc().splitlines()[-12:]}
+                    parity_ok = False
+        # the mapping object goes LAST so that a truncated tail of the line still carries it
+        line["mapping"] = line.pop("mapping")
         print(json.dumps(line), flush=True)
+        if not parity_ok:
+            print("bench.py: PARITY FAILED (see the `parity` object of the line above)", file=sys.stderr, flush=True)
+            if world == 1:
+                sys.exit(3)
     if world > 1:
         # Tearing the communicator down while captured graphs that hold NCCL kernels are alive can
         # block in ncclCommDestroy: drop the graphs, agree that everybody is done, and leave.

@@ -179,8 +179,8 @@ template <int THREADS, int GPT>
 static int launch_scatter_local(const float* means2d, const int32_t* radii, const float* rec, int C, int N,
                                 int tile_w, int tile_h, int32_t* cursors, int64_t capacity, uint64_t* dk,
                                 int32_t* overflow, size_t smem, void* stream) {
-    if (smem > 48 * 1024) {
-        // the opt-in above 48 KB is a per-device, per-function attribute and setting it is idempotent and
+    if (smem > 32 * 1024) {
+        // the opt-in above 48 KB (static + dynamic) is a per-device, per-function attribute and setting it is idempotent and
         // cheap next to a launch, so it is simply set whenever it is needed: no process-wide flag
         GSB_CUDA(cudaFuncSetAttribute(isect_scatter_local_kernel<THREADS, GPT>,
                                       cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
@@ -513,7 +513,7 @@ static int launch_segment_sort(int n, uint64_t* dk, uint64_t* tmp, const int32_t
                                int tile_n_bits, int64_t capacity, int64_t* isect_ids, int32_t* flatten_ids,
                                cudaStream_t st) {
     const int smem = KPT * SEG_THREADS * 12;
-    if (smem > 48 * 1024)    // per-device opt-in above 48 KB; idempotent, so no process-wide flag is kept
+    if (smem > 32 * 1024)    // per-device opt-in above 48 KB (static + dynamic); idempotent, so no process-wide flag is kept
         GSB_CUDA(cudaFuncSetAttribute(segment_sort_kernel<KPT>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     segment_sort_kernel<KPT><<<n, SEG_THREADS, smem, st>>>(dk, tmp, offsets, n_tiles, tile_n_bits, capacity,
                                                           isect_ids, flatten_ids);

@@ -4,10 +4,15 @@ kernel, keyed by the C-ABI entry point that launches it (bench.py puts them in `
     python tools/ncu_traffic.py gpurun_out/prof.ncu-rep profiles/traffic.json
 """
 import csv
+import datetime
 import io
 import json
+import os
 import subprocess
 import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from bench import csrc_sha  # noqa: E402  (the hash bench.py checks before quoting these numbers)
 
 ENTRY = {"project_fwd_kernel": "gsb_project_fwd", "project_bwd_kernel": "gsb_project_bwd",
          "tile_scan_kernel": "gsb_tile_scan", "isect_scatter": "gsb_isect_scatter",
@@ -29,7 +34,8 @@ for r in rows[2:]:
         continue
     b = float(r[rd]) * UNIT[units[rd]] + float(r[wr]) * UNIT[units[wr]]
     acc.setdefault(key, []).append((b, float(r[du])))
-res = {"source": rep.split("/")[-1], "note": "mean over the captured launches; ncu serialises kernels and flushes caches, so "
+res = {"source": rep.split("/")[-1], "csrc_sha": csrc_sha(),
+       "captured": datetime.datetime.utcnow().strftime("%Y-%m-%dT%H:%MZ"), "note": "mean over the captured launches; ncu serialises kernels and flushes caches, so "
        "inputs that the previous kernel left in L2 during a real step are re-read from DRAM here",
        "dram_bytes_per_launch": {k: round(sum(x[0] for x in v) / len(v)) for k, v in acc.items()},
        "ncu_us_per_launch": {k: round(sum(x[1] for x in v) / len(v), 2) for k, v in acc.items()},
