@@ -13,6 +13,15 @@ endif
 
 all: $(LIB)
 
+# make variant NAME=x EXTRA="-DFWD_PPT=1 ...": an A/B build of the kernels -> build/var_x/libgsb_x.so, used with
+# GSB_LIB=build/var_x/libgsb_x.so (gslam_b200/_lib.py); the product library is untouched
+variant:
+	@mkdir -p build/var_$(NAME)
+	@for f in $(SRCS); do b=$$(basename $$f .cu); \
+	  $(NVCC) $(NVFLAGS) $(EXTRA) -c $$f -o build/var_$(NAME)/$$b.o 2> build/var_$(NAME)/$$b.ptxas.log || (cat build/var_$(NAME)/$$b.ptxas.log; exit 1); done
+	$(NVCC) -shared -o build/var_$(NAME)/libgsb_$(NAME).so build/var_$(NAME)/*.o
+
+
 build/%.o: $(SRC_DIR)/%.cu $(wildcard $(SRC_DIR)/*.cuh) include/gsb.h
 	@mkdir -p build
 	$(NVCC) $(NVFLAGS) -c $< -o $@ 2> build/$*.ptxas.log || (cat build/$*.ptxas.log; exit 1)
@@ -22,4 +31,4 @@ $(LIB): $(OBJS)
 
 clean:
 	rm -rf build $(LIB)
-.PHONY: all clean
+.PHONY: all clean variant

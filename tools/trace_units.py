@@ -34,7 +34,7 @@ for _ in range(3):
 torch.cuda.synchronize()
 L = ctypes.CDLL(_lib.LIB_PATH)
 tiles = ((g.width + 15) // 16) * ((g.height + 15) // 16)
-buf = np.zeros(4 * 4 * tiles, dtype=np.uint64)
+buf = np.zeros(4 * 65536, dtype=np.uint64)      # GSB_TRACE_UNITS items of 4 words
 rc = getattr(L, "gsb_debug_trace_" + which)(buf.ctypes.data_as(ctypes.c_void_p), buf.size // 4)
 t = buf.reshape(-1, 4)
 t = t[t[:, 1] > 0]
