@@ -254,7 +254,7 @@ def mapping_leg(args, dev, rank, world):
     if not mine:
         mine = [rank % n_views]          # more ranks than views: replicate (never at 1/2/4/8)
     g = sc.to(dev)
-    splats = FlatSplats(g.params())
+    splats = FlatSplats(g.params(), align=world)
     opt = FusedAdam([dict(params=[p], lr=DEFAULT_LRS[nm]) for p, nm in zip(splats.params, PARAM_NAMES)],
                     capturable=True)
     mstep = MappingStep(splats, opt)
@@ -273,6 +273,24 @@ def mapping_leg(args, dev, rank, world):
 
     for _ in range(3):
         eager()
+    barrier()
+    # phase times of the step's tail from CUDA events of eager steps (max over ranks): the reduce-scatter of
+    # the gradient rows, the fused update of this rank's Gaussian range, the all-gather of the parameters
+    phases = {"reduce_scatter_ms": [], "update_ms": [], "all_gather_ms": [], "render_loss_backward_ms": []}
+    for _ in range(5):
+        mstep.phase_events = []
+        eager()
+        torch.cuda.synchronize()
+        ev_ = dict(mstep.phase_events)
+        phases["render_loss_backward_ms"].append(ev_["begin"].elapsed_time(ev_["backward_done"]))
+        phases["reduce_scatter_ms"].append(ev_["backward_done"].elapsed_time(ev_["reduce_scatter_done"]))
+        phases["update_ms"].append(ev_["reduce_scatter_done"].elapsed_time(ev_["update_done"]))
+        phases["all_gather_ms"].append(ev_["update_done"].elapsed_time(ev_["all_gather_done"]))
+    mstep.phase_events = None
+    ph = torch.tensor([statistics.median(v) for v in phases.values()], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(ph, op=dist.ReduceOp.MAX)
+    phase_ms = {k: round(float(x), 4) for k, x in zip(phases, ph)}
     barrier()
     # the step is launch-bound at one view per GPU (about 60 launches), so it is replayed as ONE CUDA
     # graph (NCCL all-reduces included); --map-eager times the plain launches instead
@@ -299,9 +317,12 @@ def mapping_leg(args, dev, rank, world):
     ms = float(t.item())
     return {"metric": "mapping views/s (8-keyframe window, full optimize_map step)", "value": n_views * 1e3 / ms,
             "unit": "views/s", "ms_per_step": ms, "steps": steps, "n_views": n_views, "n_gauss": n,
-            "views_per_rank": len(mine), "scaling": "strong",
-            "step": "render RGB+D+beta, exposure + active-NeRF NLL + 0.2 SSIM(valid), backward, "
-                    "flat-gradient all-reduce, isotropic reg, fused Adam + opacity decay", "timed_loop": mode}
+            "views_per_rank": len(mine), "scaling": "strong", "n_ranks": world,
+            "collective_ms": round(phase_ms["reduce_scatter_ms"] + phase_ms["all_gather_ms"], 4),
+            "post_reduce_ms": phase_ms["update_ms"], "eager_phases": phase_ms,
+            "step": "render RGB+D+beta, exposure + active-NeRF NLL + 0.2 SSIM(valid), backward to gradient rows, "
+                    "reduce-scatter, fused (isotropic reg + Adam + opacity decay) on this rank's Gaussians, "
+                    "all-gather of the parameters", "timed_loop": mode}
 
 
 def tracking_closure_leg(args, dev):

@@ -29,11 +29,11 @@ SIGNATURES = {
     "gsb_last_error": (ct.c_char_p, []),
     "gsb_read_i64_host": (_i, [_p, _p, _p]),
     "gsb_project_fwd": (_i, [_p] * 8 + [_i, _i, _i, _i, _f, _f, _f, _f, _i, _i] + [_p] * 5 + [_p, _i, _i] + [_p]),
-    "gsb_sh_bwd": (_i, [_p, _p, _i, _i, _p, _p, _p, _i, _i, _p, _p, _p]),
+    "gsb_sh_bwd": (_i, [_p, _p, _i, _i, _p, _p, _p, _i, _i, _p, _p, _l, _p]),
     "gsb_tile_scan": (_i, [_p, _i, _i, _i, _p, _p, _p, _p]),
     "gsb_isect_scatter": (_i, [_p, _p, _p, _i, _i, _i, _i, _p, _l, _p, _p, _p]),
     "gsb_segment_sort": (_i, [_p, _p, _p, _i, _i, _i, _i, _l, _p, _p, _p]),
-    "gsb_project_bwd": (_i, [_p] * 8 + [_i, _i, _i, _i, _f] + [_p, _p, _p, _l, _p, _i] + [_p] * 8 + [_p]),
+    "gsb_project_bwd": (_i, [_p] * 8 + [_i, _i, _i, _i, _f] + [_p, _p, _p, _l, _p, _i] + [_p] * 8 + [_l, _p] + [_p]),
     "gsb_project_bwd_det_floats": (_z, [_i, _i]),
     "gsb_pack_visible": (_i, [_p] * 4 + [_i, _i] + [_p] * 5 + [_p]),
     "gsb_scan_workspace_bytes": (_z, [_l]),
@@ -52,6 +52,7 @@ SIGNATURES = {
     "gsb_adam_multi": (_i, [_p, _i, _f, _f, _f, _i, _i, _p, _i, _f, _p, _p]),
     "gsb_composite_bwd": (_i, [_p] * 4 + [_i] * 6 + [_l] + [_p] * 6 + [_p, _p, _p, _z] + [_p]),
     "gsb_composite_bwd_det_bytes": (_z, [_l]),
+    "gsb_map_update": (_i, [_p, _i, _p, _l, _i, _l, _l, _i, _f, _i, _f, _f, _f, _f, _i, _p, _p, _p, _p, _p]),
     "gsb_vis_count": (_i, [_p, _i, _l, _p, _p]),
     "gsb_isotropic_reg": (_i, [_p, _p, _l, _f, _p, _p, _p, _p]),
     "gsb_rows_resize": (_i, [_p, _i, _l, _p, _l, _l, _p]),
@@ -64,6 +65,11 @@ SIGNATURES = {
 class RowTensor(ct.Structure):
     """gsb_row_tensor of include/gsb.h."""
     _fields_ = [("src", _p), ("dst", _p), ("add", _p), ("width", _i)]
+
+
+class MapTensor(ct.Structure):
+    """gsb_map_tensor of include/gsb.h."""
+    _fields_ = [("param", _p), ("exp_avg", _p), ("exp_avg_sq", _p), ("width", _i), ("col", _i), ("lr", _f)]
 
 
 class AdamTensor(ct.Structure):

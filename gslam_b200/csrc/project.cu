@@ -256,7 +256,7 @@ project_bwd_kernel(const float* __restrict__ means, const float* __restrict__ qu
                    float* __restrict__ v_quats, float* __restrict__ v_log_scales,
                    float* __restrict__ v_logit_opac, float* __restrict__ v_logit_colors,
                    float* __restrict__ v_log_unc, float* __restrict__ v_viewmats,
-                   float* __restrict__ det_partials) {
+                   float* __restrict__ det_partials, int64_t row_stride, float* __restrict__ v_vis) {
     __shared__ Cam cams[MAX_CAMS_SMEM];
     __shared__ float red[8][12];
     int n = blockIdx.x * blockDim.x + threadIdx.x;
@@ -271,6 +271,7 @@ project_bwd_kernel(const float* __restrict__ means, const float* __restrict__ qu
     }
     float v_mu[3] = {0.f, 0.f, 0.f}, v_Sig[9] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     float v_opac = 0.f, v_col[3] = {0.f, 0.f, 0.f}, v_beta = 0.f;
+    int n_vis = 0;          // views in which this Gaussian is visible (radii > 0)
 
     for (int c0 = 0; c0 < C; c0 += MAX_CAMS_SMEM) {
         int nc = min(MAX_CAMS_SMEM, C - c0);
@@ -282,6 +283,7 @@ project_bwd_kernel(const float* __restrict__ means, const float* __restrict__ qu
             size_t idx = (size_t)(c0 + ci) * N + n;
             float vR[9] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f}, vt[3] = {0.f, 0.f, 0.f};
             bool active = (n < N) && radii[idx] > 0;
+            n_vis += active ? 1 : 0;
             if (active) {
                 Proj p;
                 project_one(cm, mu, Sig, width, height, eps2d, -1e30f, 1e30f, -1.f, p);
@@ -417,22 +419,33 @@ project_bwd_kernel(const float* __restrict__ means, const float* __restrict__ qu
     float dotp = vqn[0] * w + vqn[1] * x + vqn[2] * y + vqn[3] * z;
     float4 vq = make_float4((vqn[0] - dotp * w) * qinv, (vqn[1] - dotp * x) * qinv,
                             (vqn[2] - dotp * y) * qinv, (vqn[3] - dotp * z) * qinv);
-    v_means[n * 3] = v_mu[0]; v_means[n * 3 + 1] = v_mu[1]; v_means[n * 3 + 2] = v_mu[2];
-    store_row4(v_quats, n, vq);
-    v_log_scales[n * 3] = v_ls[0]; v_log_scales[n * 3 + 1] = v_ls[1]; v_log_scales[n * 3 + 2] = v_ls[2];
+    // Output addressing: natural ([N,3], [N,4], ... one array per parameter) when row_stride == 0, else
+    // every pointer is the first column of its parameter inside ONE row-major [N, row_stride] gradient
+    // record (the mapping step's layout: a Gaussian's whole gradient is one contiguous row, so the
+    // rows of a Gaussian range are one contiguous block for a reduce-scatter).
+    const int64_t sm = row_stride ? row_stride : 3, sq = row_stride ? row_stride : 4, so = row_stride ? row_stride : 1;
+    v_means[n * sm] = v_mu[0]; v_means[n * sm + 1] = v_mu[1]; v_means[n * sm + 2] = v_mu[2];
+    if (row_stride) *reinterpret_cast<float4*>(v_quats + n * sq) = vq;     // 16-byte aligned by contract
+    else store_row4(v_quats, n, vq);
+    v_log_scales[n * sm] = v_ls[0]; v_log_scales[n * sm + 1] = v_ls[1]; v_log_scales[n * sm + 2] = v_ls[2];
     float o = sigmoidf_(logit_opac[n]);
-    v_logit_opac[n] = v_opac * o * (1.f - o);
+    v_logit_opac[n * so] = v_opac * o * (1.f - o);
     if (logit_colors) {     // NULL with SH colours: gsb_sh_bwd owns that gradient
 #pragma unroll
         for (int k = 0; k < 3; ++k) {
             float cc = sigmoidf_(logit_colors[n * 3 + k]);
-            v_logit_colors[n * 3 + k] = v_col[k] * cc * (1.f - cc);
+            v_logit_colors[n * sm + k] = v_col[k] * cc * (1.f - cc);
         }
     }
-    if (log_unc && v_log_unc) {
-        float bexp = expf(log_unc[n]);
-        v_log_unc[n] = (bexp >= 0.01f) ? v_beta * bexp : 0.f;
+    if (v_log_unc) {
+        float gu = 0.f;
+        if (log_unc) {
+            float bexp = expf(log_unc[n]);
+            gu = (bexp >= 0.01f) ? v_beta * bexp : 0.f;
+        }
+        if (log_unc || row_stride) v_log_unc[n * so] = gu;
     }
+    if (v_vis) v_vis[n * so] = (float)n_vis;
 }
 
 // Fixed-order sum of the per-block pose-gradient partials [C*12][n_blocks]: one warp per entry, lanes
@@ -459,8 +472,12 @@ GSB_API int gsb_project_bwd(const float* means, const float* quats, const float*
                             const float* rec, const float* v_means2d, int64_t v_means2d_stride,
                             const float* v_rec, int need_gauss_grads, float* v_means, float* v_quats,
                             float* v_log_scales, float* v_logit_opacities, float* v_logit_colors,
-                            float* v_log_unc, float* v_viewmats, float* det_partials, void* stream) {
+                            float* v_log_unc, float* v_viewmats, float* det_partials,
+                            int64_t row_stride, float* v_vis, void* stream) {
     (void)rec;
+    GSB_CHECK_ARG(row_stride == 0 || (row_stride % 4 == 0 && need_gauss_grads &&
+                                      (reinterpret_cast<uintptr_t>(v_quats) & 15) == 0));
+    GSB_CHECK_ARG(!v_vis || need_gauss_grads);
     GSB_CHECK_ARG(C >= 0 && N >= 0);
     if (C == 0 || N == 0) return 0;
     GSB_CHECK_ARG(means && quats && log_scales && logit_opacities && viewmats && Ks);
@@ -472,7 +489,7 @@ GSB_API int gsb_project_bwd(const float* means, const float* quats, const float*
         means, quats, log_scales, logit_opacities, logit_colors, log_unc, viewmats, Ks, C, N, width,
         height, eps2d, radii, v_means2d, v_means2d_stride, v_rec, need_gauss_grads, v_means, v_quats,
         v_log_scales, v_logit_opacities, v_logit_colors, v_log_unc, v_viewmats,
-        v_viewmats ? det_partials : nullptr);
+        v_viewmats ? det_partials : nullptr, row_stride, v_vis);
     GSB_LAUNCH_CHECK();
     if (v_viewmats && det_partials) {
         viewmat_partials_sum_kernel<<<C, 384, 0, gsb_stream(stream)>>>(det_partials, blocks, v_viewmats);

@@ -8,7 +8,7 @@ __global__ void __launch_bounds__(128)
 sh_bwd_kernel(const float* __restrict__ means, const float* __restrict__ coeffs, int sh_stride,
               const float* __restrict__ viewmats, const int32_t* __restrict__ radii,
               const float* __restrict__ v_rec, int C, int N, float* __restrict__ v_sh,
-              float* __restrict__ v_means) {
+              float* __restrict__ v_means, int64_t row_stride) {
     constexpr int K = (DEG + 1) * (DEG + 1);
     const int n = blockIdx.x * blockDim.x + threadIdx.x;
     if (n >= N) return;
@@ -16,6 +16,8 @@ sh_bwd_kernel(const float* __restrict__ means, const float* __restrict__ coeffs,
     const float* cf = coeffs + (size_t)n * sh_stride * 3;
     float c[K][3], vc[K][3];
     // 16-byte accesses when the row allows it (K = 4, 16 with a matching stride): see sh_colour
+    // (row_stride != 0: v_sh / v_means are columns of a row-major [N, row_stride] gradient record, a multiple
+    // of 4 floats wide -- the mapping step's layout, see gsb_project_bwd)
     const bool vec = (K * 3) % 4 == 0 && (sh_stride * 3) % 4 == 0 &&
                      ((reinterpret_cast<uintptr_t>(coeffs) | reinterpret_cast<uintptr_t>(v_sh)) & 15) == 0;
     if (vec) {
@@ -76,7 +78,7 @@ sh_bwd_kernel(const float* __restrict__ means, const float* __restrict__ coeffs,
         vmu[1] += (gy - dotp * y) * inv;
         vmu[2] += (gz - dotp * z) * inv;
     }
-    float* out = v_sh + (size_t)n * sh_stride * 3;
+    float* out = v_sh + (size_t)n * (row_stride ? (size_t)row_stride : (size_t)sh_stride * 3);
     if (vec) {
         float4* o4 = reinterpret_cast<float4*>(out);
 #pragma unroll
@@ -93,21 +95,21 @@ sh_bwd_kernel(const float* __restrict__ means, const float* __restrict__ coeffs,
         for (int ch = 0; ch < 3; ++ch) out[k * 3 + ch] = 0.f;
     if (v_means) {
 #pragma unroll
-        for (int j = 0; j < 3; ++j) v_means[n * 3 + j] += vmu[j];
+        for (int j = 0; j < 3; ++j) v_means[n * (row_stride ? row_stride : 3) + j] += vmu[j];
     }
 }
 
 GSB_API int gsb_sh_bwd(const float* means, const float* sh_coeffs, int sh_degree, int sh_stride,
                        const float* viewmats, const int32_t* radii, const float* v_rec, int C, int N,
-                       float* v_sh, float* v_means, void* stream) {
-    GSB_CHECK_ARG(C >= 0 && N >= 0);
+                       float* v_sh, float* v_means, int64_t row_stride, void* stream) {
+    GSB_CHECK_ARG(C >= 0 && N >= 0 && row_stride >= 0 && row_stride % 4 == 0);
     if (N == 0) return 0;
     GSB_CHECK_ARG(means && sh_coeffs && viewmats && radii && v_rec && v_sh);
     GSB_CHECK_ARG(sh_degree >= 0 && sh_degree <= 3 && sh_stride >= (sh_degree + 1) * (sh_degree + 1));
     const int blocks = (N + 127) / 128;
 #define GSB_SH(D)                                                                                   \
     sh_bwd_kernel<D><<<blocks, 128, 0, gsb_stream(stream)>>>(means, sh_coeffs, sh_stride, viewmats, \
-                                                             radii, v_rec, C, N, v_sh, v_means)
+                                                             radii, v_rec, C, N, v_sh, v_means, row_stride)
     switch (sh_degree) {
         case 0: GSB_SH(0); break;
         case 1: GSB_SH(1); break;

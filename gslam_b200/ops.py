@@ -27,9 +27,28 @@ CSTRIDE = 32   # GSB_CSTRIDE: one per-tile counter per 128-byte line
 # bench.py sets this to a zeroed int64[1] CUDA tensor to collect P (pairs evaluated); None otherwise
 pair_counter: Optional[Tensor] = None
 
-# extra floats allocated behind the flat [15 N] gradient buffer of _Project.backward: the mapping step
-# parks its visibility counts and loss scalars there so that ONE all-reduce carries everything
-grad_tail_floats: int = 0
+# Row-major gradient record of the mapping step.  When `grad_rows_out` is set (a zero-padded float32
+# [N_pad >= N, row_stride] tensor), _Project.backward writes the six Gaussian gradients AND the per-Gaussian
+# visibility count into it, one contiguous row per Gaussian, and hands autograd no gradient for the six
+# parameters (`grad_rows_written` is raised instead): the rows of a Gaussian range are one contiguous block,
+# which is what a reduce-scatter over the ranks of a view-sharded step needs, and the fused update kernel
+# (gsb_map_update) reads the whole gradient of a Gaussian with four 16-byte loads.
+grad_rows_out: Optional[Tensor] = None
+grad_rows_written: bool = False
+
+
+class RowLayout:
+    """Columns of one gradient row for colours of 3 * K floats per Gaussian (K = 1: the reference's
+    [N,3] logit colours; K = (deg+1)^2 .. : SH coefficients [N,K,3]).  quats first: 16-byte aligned."""
+
+    def __init__(self, K: int = 1):
+        self.K = int(K)
+        self.quats, self.means, self.opacities, self.scales, self.unc, self.colors = 0, 4, 7, 8, 11, 12
+        self.vis = 12 + 3 * self.K
+        self.stride = -(-(self.vis + 1) // 4) * 4
+        # in PARAM_NAMES order: means, quats, scales, opacities, colors, log_uncertainties
+        self.cols = (self.means, self.quats, self.scales, self.opacities, self.colors, self.unc)
+        self.widths = (3, 4, 3, 1, 3 * self.K, 1)
 
 
 # Deterministic accumulation (bit-identical gradients and loss values from run to run): the float
@@ -139,10 +158,37 @@ class _Project(torch.autograd.Function):
         need = ctx.needs_input_grad
         need_gauss = any(need[:6])
         need_view = need[6]
+        sh = ctx.sh_degree is not None
+        rows = grad_rows_out if need_gauss else None
+        if rows is not None:
+            # the mapping step's row layout: everything goes into the caller's [N_pad, stride] record
+            global grad_rows_written
+            lay = RowLayout(logit_colors.shape[1] if sh else 1)
+            if not (rows.is_cuda and rows.dtype == torch.float32 and rows.is_contiguous() and rows.dim() == 2
+                    and rows.shape[0] >= N and rows.shape[1] == lay.stride):
+                raise ValueError(f"ops.grad_rows_out must be a contiguous float32 [>= {N}, {lay.stride}] CUDA tensor")
+            v_view = torch.zeros(C, 4, 4, dtype=torch.float32, device=dev) if need_view else None
+            det_part = det_scratch(lib().gsb_project_bwd_det_floats(C, N), dev) if (ctx.det and need_view) else None
+            base = rows.data_ptr()
+            col = lambda c: base + 4 * c   # noqa: E731
+            call("gsb_project_bwd",
+                 ptr(means), ptr(quats), ptr(log_scales), ptr(logit_opacities),
+                 None if sh else ptr(logit_colors),
+                 ptr(log_unc), ptr(viewmats), ptr(Ks), C, N, width, height, eps2d, ptr(radii), ptr(rec),
+                 ptr(g_means2d), m2_stride, ptr(g_rec), 1, col(lay.means), col(lay.quats), col(lay.scales),
+                 col(lay.opacities), None if sh else col(lay.colors), col(lay.unc), ptr(v_view), ptr(det_part),
+                 lay.stride, col(lay.vis), stream())
+            if sh:
+                call("gsb_sh_bwd", ptr(means), ptr(logit_colors), ctx.sh_degree, logit_colors.shape[1],
+                     ptr(viewmats), ptr(radii), ptr(g_rec), C, N, col(lay.colors), col(lay.means), lay.stride,
+                     stream())
+            grad_rows_written = True
+            return (None, None, None, None, None, None, v_view, None, None, None, None, None, None, None, None,
+                    None, None, None, None)
         if need_gauss:
             # one flat buffer, means|quats|scales|opacities|colors|log_unc, so that a
             # view-sharded mapping step can all-reduce the six gradients in ONE call
-            flat = torch.empty(N * 15 + grad_tail_floats, dtype=torch.float32, device=dev)
+            flat = torch.empty(N * 15, dtype=torch.float32, device=dev)
             v_means = flat[0:3 * N].view(N, 3)
             v_quats = flat[3 * N:7 * N].view(N, 4)
             v_scales = flat[7 * N:10 * N].view(N, 3)
@@ -154,7 +200,6 @@ class _Project(torch.autograd.Function):
         else:
             v_means = v_quats = v_scales = v_opac = v_colors = v_unc = None
         v_view = torch.zeros(C, 4, 4, dtype=torch.float32, device=dev) if need_view else None
-        sh = ctx.sh_degree is not None
         det_part = None
         if ctx.det and need_view:
             det_part = det_scratch(lib().gsb_project_bwd_det_floats(C, N), dev)
@@ -165,11 +210,11 @@ class _Project(torch.autograd.Function):
                 ptr(log_unc), ptr(viewmats), ptr(Ks), C, N, width, height, eps2d, ptr(radii), ptr(rec),
                 ptr(g_means2d), m2_stride, ptr(g_rec), int(need_gauss), ptr(v_means), ptr(v_quats),
                 ptr(v_scales), ptr(v_opac), None if sh else ptr(v_colors), ptr(v_unc), ptr(v_view),
-                ptr(det_part), stream())
+                ptr(det_part), 0, None, stream())
         if sh and need_gauss:
             v_colors = torch.empty_like(logit_colors)
             call("gsb_sh_bwd", ptr(means), ptr(logit_colors), ctx.sh_degree, logit_colors.shape[1],
-                 ptr(viewmats), ptr(radii), ptr(g_rec), C, N, ptr(v_colors), ptr(v_means), stream())
+                 ptr(viewmats), ptr(radii), ptr(g_rec), C, N, ptr(v_colors), ptr(v_means), 0, stream())
         grads = [v_means, v_quats, v_scales, v_opac, v_colors,
                  v_unc if log_unc is not None else None]
         grads = [g if n else None for g, n in zip(grads, need[:6])]

@@ -14,7 +14,7 @@ from typing import Optional
 
 import torch
 
-from ._lib import AdamTensor, call, stream
+from ._lib import AdamTensor, MapTensor, call, stream
 
 
 class FusedAdam(torch.optim.Optimizer):
@@ -79,3 +79,48 @@ class FusedAdam(torch.optim.Optimizer):
                      decay_idx, vc, vis_div, decay,
                      self._dev_step.data_ptr() if self.capturable else None, stream())
         return loss
+
+    @torch.no_grad()
+    def step_rows(self, params, rows: torch.Tensor, layout, n0: int, n1: int,
+                  vis_out: Optional[torch.Tensor] = None, scales_index: int = -1, iso_weight: float = 0.0,
+                  decay_index: int = -1, decay: float = 0.995) -> torch.Tensor:
+        """The mapping step's fused update (gsb_map_update) of the Gaussians [n0, n1): `params` are the six
+        splat parameters in `mapping.PARAM_NAMES` order, their gradient is `rows[n, layout.cols[k] + j]`
+        (ops.RowLayout) and rows[n, layout.vis] the visibility count.  Adds the isotropic-regulariser
+        gradient on params[scales_index], runs Adam with this optimizer's state and learning rates, decays
+        params[decay_index] where the count is above one, writes the counts to vis_out (int32).  Returns
+        the range's unweighted isotropic loss as a [1] tensor.  One launch; capturable like `step()`."""
+        from . import ops
+        lrs, hyper = {}, {}
+        for group in self.param_groups:
+            for p in group["params"]:
+                lrs[id(p)] = group["lr"]
+                hyper[id(p)] = (tuple(group["betas"]), group["eps"])
+        dev = rows.device
+        if params[0].shape[0] == 0:
+            return torch.zeros(1, dtype=torch.float32, device=dev)
+        if len({hyper.get(id(p)) for p in params}) != 1:
+            raise RuntimeError("FusedAdam.step_rows: the splat parameters must share betas and eps")
+        betas, eps = hyper[id(params[0])]
+        arr = (MapTensor * len(params))()
+        step = 0
+        for k, p in enumerate(params):
+            if id(p) not in lrs:
+                raise RuntimeError("FusedAdam.step_rows: parameter is not in this optimizer")
+            if not (p.is_cuda and p.dtype == torch.float32 and p.is_contiguous()):
+                raise RuntimeError("FusedAdam needs contiguous float32 CUDA parameters")
+            st = self._state(p)
+            if not self.capturable:
+                st["step"] += 1
+                step = int(st["step"])
+            width = p.numel() // max(p.shape[0], 1) if p.shape[0] else layout.widths[k]
+            arr[k] = MapTensor(p.data_ptr(), st["exp_avg"].data_ptr(), st["exp_avg_sq"].data_ptr(), width,
+                               layout.cols[k], lrs[id(p)])
+        iso = torch.zeros(1, dtype=torch.float32, device=dev)
+        part = ops.det_scratch((max(n1 - n0, 1) + 255) // 256, dev) if ops.deterministic else None
+        call("gsb_map_update", ct.cast(arr, ct.c_void_p), len(params), rows.data_ptr(), rows.shape[1], layout.vis,
+             n0, n1, scales_index, float(iso_weight), decay_index, float(decay), betas[0], betas[1], eps, step,
+             self._dev_step.data_ptr() if self.capturable else None,
+             vis_out.data_ptr() if vis_out is not None else None, iso.data_ptr(),
+             part.data_ptr() if part is not None else None, stream())
+        return iso

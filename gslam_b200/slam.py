@@ -265,7 +265,7 @@ class Slam:
                     res.n_touched = torch.cat([res.n_touched, res.n_touched.new_zeros(
                         res.n_touched.shape[0], n_dup + n_split)], dim=1)
             else:
-                self.opt.step(decay_param=self.splats.params[3], vis_count=res.vis_count, decay=c.opacity_decay)
+                self.step.apply_pending()        # nothing was re-created: the iteration's update after all
         if self.pose_opt is not None:
             self.pose_opt.step()            # keyframe 0 is in no group: its pose stays fixed (:604-611)
         return res, changed

@@ -18,15 +18,8 @@ from torch import Tensor
 
 from . import ops
 from ._lib import RowTensor, call, ptr, stream
-from .mapping import PARAM_NAMES, PARAM_WIDTH, FlatSplats
+from .mapping import PARAM_NAMES, FlatSplats, _round_up
 
-
-def _views(flat: Tensor, n: int) -> List[Tensor]:
-    out, o = [], 0
-    for w in PARAM_WIDTH:
-        out.append(flat[o:o + w * n].view((n, w) if w > 1 else (n,)))
-        o += w * n
-    return out
 
 
 def _state_tensors(optimizer, params: Sequence[Tensor], key: str) -> List[Optional[Tensor]]:
@@ -47,6 +40,7 @@ def resize_splats(splats: FlatSplats, optimizer, keep_mask: Optional[Tensor] = N
     old_params = list(splats.params)
     n_old = splats.n
     dev = splats.flat.device
+    W = splats.widths
     cum, n_keep = None, n_old
     if keep_mask is not None:
         assert keep_mask.shape == (n_old,)
@@ -58,23 +52,25 @@ def resize_splats(splats: FlatSplats, optimizer, keep_mask: Optional[Tensor] = N
         n_add = new_params["means"].shape[0]
         for k, name in enumerate(PARAM_NAMES):
             t = new_params[name].detach().to(dev, torch.float32).contiguous()
-            assert t.shape[0] == n_add and t.numel() == n_add * PARAM_WIDTH[k], (name, tuple(t.shape))
+            assert t.shape[0] == n_add and t.numel() == n_add * W[k], (name, tuple(t.shape))
             adds[k] = t
     n_new = n_keep + n_add
 
-    new_flat = torch.empty(15 * n_new, device=dev, dtype=torch.float32)
-    new_views = _views(new_flat, n_new)
+    # same block layout as FlatSplats: six blocks of `cap` rows (n rounded up to the rank count), padding zero
+    cap_new = _round_up(n_new, splats.align)
+    new_flat = torch.zeros(sum(W) * cap_new, device=dev, dtype=torch.float32)
+    new_views = FlatSplats.views(new_flat, n_new, cap_new, splats.K)
     exp_avg, exp_avg_sq = _state_tensors(optimizer, old_params, "exp_avg"), _state_tensors(optimizer, old_params, "exp_avg_sq")
     has_state = any(t is not None for t in exp_avg)
-    m_views = _views(torch.zeros(15 * n_new, device=dev), n_new) if has_state else [None] * 6
-    v_views = _views(torch.zeros(15 * n_new, device=dev), n_new) if has_state else [None] * 6
+    m_views = FlatSplats.views(torch.zeros(sum(W) * cap_new, device=dev), n_new, cap_new, splats.K) if has_state else [None] * 6
+    v_views = FlatSplats.views(torch.zeros(sum(W) * cap_new, device=dev), n_new, cap_new, splats.K) if has_state else [None] * 6
 
     rows = []
     for k in range(6):
-        rows.append((old_params[k].detach(), new_views[k], adds[k], PARAM_WIDTH[k]))
+        rows.append((old_params[k].detach(), new_views[k], adds[k], W[k]))
         for src, dst in ((exp_avg[k], m_views[k]), (exp_avg_sq[k], v_views[k])):
             if src is not None:
-                rows.append((src.contiguous(), dst, None, PARAM_WIDTH[k]))
+                rows.append((src.contiguous(), dst, None, W[k]))
     arr = (RowTensor * len(rows))()
     for i, (src, dst, add, w) in enumerate(rows):
         arr[i] = RowTensor(ptr(src) if n_old else None, ptr(dst) if n_new else None, ptr(add), w)
@@ -82,7 +78,7 @@ def resize_splats(splats: FlatSplats, optimizer, keep_mask: Optional[Tensor] = N
         call("gsb_rows_resize", ct.cast(arr, ct.c_void_p), len(rows), n_old, ptr(cum), n_keep, n_add, stream())
 
     # re-key: new leaf parameters (views of the new flat buffer), same state dict objects
-    splats.flat, splats.n = new_flat, n_new
+    splats.flat, splats.n, splats.cap = new_flat, n_new, cap_new
     splats.params = [v.requires_grad_(True) for v in new_views]
     if optimizer is not None:
         by_old = {id(p): k for k, p in enumerate(old_params)}

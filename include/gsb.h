@@ -75,7 +75,12 @@ int gsb_project_fwd(const float* means, const float* quats, const float* log_sca
  * logit_colors = v_logit_colors = NULL and call gsb_sh_bwd afterwards.
  * Deterministic mode: det_partials (NULL = atomics) is scratch of gsb_project_bwd_det_floats(C, N)
  * floats; the per-block pose-gradient sums go there and are added in a fixed order, so v_viewmats is
- * bit-identical from run to run. */
+ * bit-identical from run to run.
+ * Row layout (the mapping step): with row_stride > 0 (a multiple of 4) every v_* pointer of the six
+ * Gaussian gradients is the FIRST COLUMN of that parameter inside one row-major [N, row_stride] float
+ * record (element k of Gaussian n at ptr[n * row_stride + k]; v_quats 16-byte aligned; v_log_unc is
+ * written as 0 when log_unc is NULL), so a Gaussian's whole gradient is one contiguous row; v_vis
+ * (may be NULL, addressed like v_logit_opacities) receives the number of views with radii > 0. */
 size_t gsb_project_bwd_det_floats(int C, int N);
 int gsb_project_bwd(const float* means, const float* quats, const float* log_scales,
                     const float* logit_opacities, const float* logit_colors,
@@ -86,14 +91,16 @@ int gsb_project_bwd(const float* means, const float* quats, const float* log_sca
                     int need_gauss_grads,
                     float* v_means, float* v_quats, float* v_log_scales,
                     float* v_logit_opacities, float* v_logit_colors, float* v_log_unc,
-                    float* v_viewmats, float* det_partials, void* stream);
+                    float* v_viewmats, float* det_partials, int64_t row_stride, float* v_vis,
+                    void* stream);
 
 /* Backward of the SH colours of gsb_project_fwd: v_sh[N, sh_stride, 3] is overwritten (summed over
  * cameras), the view-direction term is ADDED to v_means[N,3] (may be NULL), so call it after
- * gsb_project_bwd on the same stream.  The camera centre is treated as a constant. */
+ * gsb_project_bwd on the same stream.  The camera centre is treated as a constant.  row_stride > 0:
+ * v_sh and v_means are columns of the row-major gradient record of gsb_project_bwd (same stride). */
 int gsb_sh_bwd(const float* means, const float* sh_coeffs, int sh_degree, int sh_stride,
                const float* viewmats, const int32_t* radii, const float* v_rec, int C, int N,
-               float* v_sh, float* v_means, void* stream);
+               float* v_sh, float* v_means, int64_t row_stride, void* stream);
 
 /* K3: packed projection (reference gslam/rasterization.py:390-419).  Two calls:
  * gsb_project_fwd (unpacked) then gsb_pack_visible compacts the rows with
@@ -249,6 +256,31 @@ int gsb_adam_multi(const gsb_adam_tensor* tensors_host, int n_tensors, float bet
 int gsb_vis_count(const int32_t* radii, int C, int64_t N, int32_t* vis_count, void* stream);
 int gsb_isotropic_reg(const float* log_scales, const int32_t* vis_count, int64_t N, float weight,
                       float* v_log_scales, float* loss_sum, float* det_partials, void* stream);
+
+/* ---- the per-Gaussian tail of a mapping iteration, fused and range-limited ----------------------
+ * One launch over the Gaussians [n0, n1): visibility = grad_rows[n, vis_col] (the reduced view count
+ * written by gsb_project_bwd's v_vis) -> vis_count_out[n] (int32, may be NULL); on tensor
+ * `scales_tensor` (width 3, -1: none) the isotropic-regulariser gradient of gslam/backend.py:286-296
+ * is added where visibility > 0 and the unweighted sum of |exp(s) - exp(mean s)| is added to
+ * *iso_loss_sum (may be NULL; det_partials: scratch of ceil((n1-n0)/256) floats for a fixed-order sum
+ * that overwrites it); then torch.optim.Adam (defaults; `step` / `step_dev` as gsb_adam_multi) on
+ * every listed tensor, gradient of element k of Gaussian n at grad_rows[n * row_stride + col + k];
+ * tensor `decay_tensor` (-1: none) is multiplied by `decay` where visibility > 1
+ * (gslam/backend.py:356-359).  A view-sharded step calls it on its own range after the
+ * reduce-scatter of the rows; one GPU calls it on [0, N). */
+typedef struct {
+    float* param;        /* [N, width] */
+    float* exp_avg;
+    float* exp_avg_sq;
+    int width;
+    int col;             /* first column of this tensor's gradient in a row */
+    float lr;
+} gsb_map_tensor;
+int gsb_map_update(const gsb_map_tensor* tensors_host, int n_tensors, const float* grad_rows,
+                   int64_t row_stride, int vis_col, int64_t n0, int64_t n1, int scales_tensor,
+                   float iso_weight, int decay_tensor, float decay, float beta1, float beta2, float eps,
+                   int step, int32_t* step_dev, int32_t* vis_count_out, float* iso_loss_sum,
+                   float* det_partials, void* stream);
 
 /* ---- densify / prune surgery ------------------------------------------------
  * Replaces the per-tensor `value[keep_mask]` / `torch.cat` loops of gslam/pruning.py:10-53 and

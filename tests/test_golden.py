@@ -65,7 +65,7 @@ def test_cuda_path_matches_golden(cuda):
     total, photo = photometric_ssim_loss(out.render, gt, ex, 0.2, "mapping")
     total = total + 1e-6 * edge_aware_tv(out.depthmaps, out.rgbs, out.alphas[..., 0] > 0.4)
     total.backward()
-    iso = add_isotropic_grad_(ps[2].grad, ps[2], out.radii.sum(0) > 0, 5e-4)
+    iso = add_isotropic_grad_(ps[2].grad, ps[2], (out.radii > 0).sum(0).to(torch.int32), 5e-4)
     assert abs(float(total) + 5e-4 * float(iso) - float(gold["loss_total"])) < 1e-4 * abs(float(gold["loss_total"]))
     assert abs(float(photo) - float(gold["loss_photo"])) < 1e-4 * abs(float(gold["loss_photo"]))
     names = ["g_means", "g_quats", "g_scales", "g_opacities", "g_colors", "g_log_unc"]

@@ -62,13 +62,15 @@ def test_prune_then_append_matches_torch_indexing(cuda, capturable):
         st = opt.state[p]
         assert torch.equal(st["exp_avg"][:-321], M2[k]) and bool((st["exp_avg"][-321:] == 0).all())
         assert torch.equal(st["exp_avg_sq"][:-321], V2[k]) and bool((st["exp_avg_sq"][-321:] == 0).all())
-    # the flat layout survived: one render + backward fills a single [15 N] gradient buffer and Adam steps
+    # the flat layout survived: the parameters are the leading rows of six blocks of ONE buffer, one render +
+    # backward fills a single [15 N] gradient buffer, and Adam steps
+    assert all(p.data_ptr() == b.data_ptr() for p, b in zip(splats.params, splats.blocks()))
     out = rasterization(*splats.params[:5], sc.viewmats, sc.Ks, sc.width, sc.height, packed=False,
                         render_mode="RGB+D", log_uncertainties=splats.params[5],
                         backgrounds=torch.zeros(1, 3, device=cuda))
     out.render.sum().backward()
-    flat_g = splats.flat_grad()
-    assert flat_g.numel() == 15 * splats.n and flat_g.data_ptr() == splats.params[0].grad.data_ptr()
+    g0 = splats.params[0].grad
+    assert all(g.untyped_storage().data_ptr() == g0.untyped_storage().data_ptr() for g in (p.grad for p in splats.params))
     before = splats.flat.clone()
     opt.step()
     assert not torch.equal(before, splats.flat)

@@ -13,7 +13,7 @@ dev = torch.device("cuda:0")
 sc = make_scene(n, n_views, "tum", 1.0)
 g = sc.to(dev)
 splats = FlatSplats(g.params())
-opt = FusedAdam([dict(params=[p], lr=DEFAULT_LRS[nm]) for p, nm in zip(splats.params, PARAM_NAMES)])
+opt = FusedAdam([dict(params=[p], lr=DEFAULT_LRS[nm]) for p, nm in zip(splats.params, PARAM_NAMES)], capturable=True)
 step = MappingStep(splats, opt)
 gt = target_images(n_views, sc.height, sc.width).to(dev)
 exposure = torch.zeros(n_views, 2, device=dev)
