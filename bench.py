@@ -48,6 +48,7 @@ def parse():
     ap.add_argument("--map-gauss", type=int, default=500_000)
     ap.add_argument("--no-mapping", action="store_true")
     ap.add_argument("--map-eager", action="store_true")
+    ap.add_argument("--map-comm", default="auto", choices=["auto", "nccl", "nvls"])
     ap.add_argument("--track-frames", type=int, default=12)
     ap.add_argument("--slam-frames", type=int, default=60)
     ap.add_argument("--no-sequence", action="store_true")
@@ -254,10 +255,11 @@ def mapping_leg(args, dev, rank, world):
     if not mine:
         mine = [rank % n_views]          # more ranks than views: replicate (never at 1/2/4/8)
     g = sc.to(dev)
-    splats = FlatSplats(g.params(), align=world)
+    want_nvls = world > 1 and args.map_comm != "nccl"
+    splats = FlatSplats(g.params(), align=4 * world, symmetric=dist.group.WORLD if want_nvls else None)
     opt = FusedAdam([dict(params=[p], lr=DEFAULT_LRS[nm]) for p, nm in zip(splats.params, PARAM_NAMES)],
                     capturable=True)
-    mstep = MappingStep(splats, opt)
+    mstep = MappingStep(splats, opt, comm=args.map_comm)
     vm, K = g.viewmats[mine].contiguous(), g.Ks[mine].contiguous()
     gt = target_images(n_views, sc.height, sc.width)[mine].to(dev)
     exposure = torch.zeros(len(mine), 2, device=dev)
@@ -318,6 +320,10 @@ def mapping_leg(args, dev, rank, world):
     return {"metric": "mapping views/s (8-keyframe window, full optimize_map step)", "value": n_views * 1e3 / ms,
             "unit": "views/s", "ms_per_step": ms, "steps": steps, "n_views": n_views, "n_gauss": n,
             "views_per_rank": len(mine), "scaling": "strong", "n_ranks": world,
+            "comm": "none (one rank)" if world == 1 else (
+                "nvls: one kernel = in-switch reduce-scatter (multimem.ld_reduce) + update + multicast all-gather "
+                "(multimem.st), two device barriers" if mstep._nvls is not None else
+                "nccl: reduce_scatter_tensor + update kernel + coalesced all_gather_into_tensor"),
             "collective_ms": round(phase_ms["reduce_scatter_ms"] + phase_ms["all_gather_ms"], 4),
             "post_reduce_ms": phase_ms["update_ms"], "eager_phases": phase_ms,
             "step": "render RGB+D+beta, exposure + active-NeRF NLL + 0.2 SSIM(valid), backward to gradient rows, "

@@ -43,6 +43,17 @@ DEFAULT_LRS = dict(means=1.6e-3, quats=5e-3, scales=5e-3, opacities=2.5e-2, colo
                    log_uncertainties=2.5e-3)
 
 
+def symmetric_zeros(numel: int, dtype, device, group):
+    """A zeroed torch symmetric-memory tensor and its rendezvous handle (collective over `group`: every
+    rank calls it with the same size, in the same order).  The handle carries the peers' mapped addresses,
+    the NVLS multicast address (0 if the fabric has none) and a device-side barrier."""
+    import torch.distributed._symmetric_memory as symm_mem
+    t = symm_mem.empty(max(int(numel), 1), dtype=dtype, device=device)
+    h = symm_mem.rendezvous(t, group=group if group is not None else dist.group.WORLD)
+    t.zero_()
+    return t[:numel], h
+
+
 def shard_views(n_views: int, rank: int, world: int) -> List[int]:
     """Views of the window rendered by `rank`: window[rank::world]."""
     return list(range(rank, n_views, world))
@@ -63,7 +74,10 @@ class FlatSplats:
     all-gather of the updated parameters); a parameter is the first n rows of its block.  Colours are
     [N,3] (the reference) or SH coefficients [N,K,3] (extension, BASELINE cfg4)."""
 
-    def __init__(self, tensors: Sequence[Tensor], align: int = 1):
+    def __init__(self, tensors: Sequence[Tensor], align: int = 1, symmetric=None):
+        """symmetric: a process group -- the flat buffer is then a torch symmetric-memory allocation shared with
+        the group's ranks (same size everywhere; `self.symm` is its handle), which lets the fused update
+        kernel multicast-store the updated parameters into every GPU's copy (MappingStep, NVLS path)."""
         n = tensors[0].shape[0]
         dev, dt = tensors[0].device, tensors[0].dtype
         colors = tensors[4]
@@ -72,7 +86,11 @@ class FlatSplats:
         self.align = max(int(align), 1)
         self.n = n
         self.cap = _round_up(n, self.align)
-        self.flat = torch.zeros(sum(self.widths) * self.cap, device=dev, dtype=dt)
+        self.symm = None
+        if symmetric is not None:
+            self.flat, self.symm = symmetric_zeros(sum(self.widths) * self.cap, dt, dev, symmetric)
+        else:
+            self.flat = torch.zeros(sum(self.widths) * self.cap, device=dev, dtype=dt)
         self.params: List[Tensor] = []
         for k, v in enumerate(self.views(self.flat, n, self.cap, self.K)):
             v.copy_(tensors[k].detach().reshape(v.shape))
@@ -202,7 +220,11 @@ class MappingStep:
                  loss_fn: Optional[Callable] = None, ssim_weight: float = 0.2,
                  isotropic_weight: float = 5e-4, opacity_decay: float = 0.995, depth_tv_weight: float = 0.0,
                  group=None, sh_degree: Optional[int] = None, update_fn: Optional[Callable] = None,
-                 collect_grads: Optional[Callable] = None):
+                 collect_grads: Optional[Callable] = None, comm: str = "auto"):
+        """comm (more than one rank): "nccl" = reduce-scatter / all-gather collectives around the update
+        kernel; "nvls" = ONE kernel that does all three over NVLink multicast (needs FlatSplats(symmetric=group)
+        and a fabric with multicast: torch symmetric memory's multicast_ptr); "auto" = nvls when the splats
+        are symmetric and multicast is there, else nccl."""
         if render_fn is None:
             from .rasterization import rasterization as render_fn
         if loss_fn is None:
@@ -215,6 +237,9 @@ class MappingStep:
         self.tv_w = depth_tv_weight
         self.sh_degree = sh_degree
         self.retain_means2d_grad = False      # out.means2d.retain_grad() of gslam/backend.py:326 (densification)
+        if comm not in ("auto", "nccl", "nvls"):
+            raise ValueError(comm)
+        self.comm = comm
         self.phase_events: Optional[list] = None   # bench.py: [(name, start, end)] CUDA events of an eager step
         self._buf_key = None
         self._pending = None
@@ -225,9 +250,23 @@ class MappingStep:
         dev = sp.flat.device
         key = (sp.cap, lay.stride, world, dev)
         if key != self._buf_key:
-            self._rows = torch.zeros(sp.cap, lay.stride, dtype=torch.float32, device=dev)
-            self._vis = torch.zeros(sp.cap, dtype=torch.int32, device=dev)
-            self._stats = torch.zeros(world, 4, dtype=torch.float32, device=dev)
+            self._nvls = None
+            use_nvls = world > 1 and self.comm != "nccl" and sp.symm is not None and \
+                bool(getattr(sp.symm, "multicast_ptr", 0)) and self.update_fn is fused_update
+            if self.comm == "nvls" and world > 1 and not use_nvls:
+                raise RuntimeError("MappingStep(comm='nvls') needs FlatSplats(symmetric=group) on a fabric with "
+                                   "NVLink multicast and the default update_fn")
+            if use_nvls:
+                rows, h_rows = symmetric_zeros(sp.cap * lay.stride, torch.float32, dev, self.group)
+                vis, h_vis = symmetric_zeros(sp.cap, torch.int32, dev, self.group)
+                stats, h_stats = symmetric_zeros(world * 4, torch.float32, dev, self.group)
+                self._rows, self._vis, self._stats = rows.view(sp.cap, lay.stride), vis, stats.view(world, 4)
+                self._nvls = (h_rows, h_vis, h_stats)
+                self._mc_scratch = torch.zeros(sp.cap // world // 256 + 8, dtype=torch.float32, device=dev)
+            else:
+                self._rows = torch.zeros(sp.cap, lay.stride, dtype=torch.float32, device=dev)
+                self._vis = torch.zeros(sp.cap, dtype=torch.int32, device=dev)
+                self._stats = torch.zeros(world, 4, dtype=torch.float32, device=dev)
             self._buf_key = key
         return self._rows, self._vis, self._stats
 
@@ -300,6 +339,21 @@ class MappingStep:
             self._pending = (rows, lay, vis)
             return MappingStepResult(mine[0], mine[1], out.radii, out.n_touched, vis_count, out)
         self._pending = None
+        if world > 1 and self._nvls is not None:
+            # ONE kernel = reduce-scatter (in-switch sums of the rows) + update + all-gather (multicast stores),
+            # between two cross-GPU barriers: every rank's rows written before, every store visible after
+            h_rows, h_vis, h_stats = self._nvls
+            h_rows.barrier()
+            self._mark("reduce_scatter_done")
+            self.opt.step_rows_mc(P, sp, rows, h_rows.multicast_ptr, lay, rank * per, min((rank + 1) * per, n)
+                                  if rank * per < n else rank * per, h_vis.multicast_ptr, mine, h_stats.multicast_ptr,
+                                  rank, self._mc_scratch, scales_index=2, iso_weight=self.iso_w, decay_index=3,
+                                  decay=self.decay)
+            self._mark("update_done")
+            h_rows.barrier()
+            tot = stats_all.sum(dim=0)
+            self._mark("all_gather_done")
+            return MappingStepResult(tot[0] + self.iso_w * tot[2], tot[1], out.radii, out.n_touched, vis[:n], out)
         if world > 1:
             chunk = rows[rank * per:(rank + 1) * per]
             if dist.get_backend(self.group) == "nccl":

@@ -124,3 +124,36 @@ class FusedAdam(torch.optim.Optimizer):
              vis_out.data_ptr() if vis_out is not None else None, iso.data_ptr(),
              part.data_ptr() if part is not None else None, stream())
         return iso
+
+    @torch.no_grad()
+    def step_rows_mc(self, params, splats, rows: torch.Tensor, rows_mc: int, layout, n0: int, n1: int, vis_mc: int,
+                     stats_in: torch.Tensor, stats_mc: int, rank: int, scratch: torch.Tensor,
+                     scales_index: int = -1, iso_weight: float = 0.0, decay_index: int = -1,
+                     decay: float = 0.995) -> None:
+        """`step_rows` as ONE kernel that is also the reduce-scatter and the all-gather (gsb_map_update_mc):
+        rows_mc / vis_mc / stats_mc are NVLink-multicast addresses of symmetric allocations, `splats.flat` is
+        a symmetric allocation too (splats.symm.multicast_ptr).  The caller provides the barriers."""
+        import ctypes
+        lrs, hyper = {}, {}
+        for group in self.param_groups:
+            for p in group["params"]:
+                lrs[id(p)] = group["lr"]
+                hyper[id(p)] = (tuple(group["betas"]), group["eps"])
+        betas, eps = hyper[id(params[0])]
+        arr = (MapTensor * len(params))()
+        mc = (ctypes.c_uint64 * len(params))()
+        step = 0
+        flat_mc = int(splats.symm.multicast_ptr)
+        base = splats.flat.data_ptr()
+        for k, p in enumerate(params):
+            st = self._state(p)
+            if not self.capturable:
+                st["step"] += 1
+                step = int(st["step"])
+            arr[k] = MapTensor(p.data_ptr(), st["exp_avg"].data_ptr(), st["exp_avg_sq"].data_ptr(), layout.widths[k],
+                               layout.cols[k], lrs[id(p)])
+            mc[k] = flat_mc + (p.data_ptr() - base)
+        call("gsb_map_update_mc", ct.cast(arr, ct.c_void_p), ct.cast(mc, ct.c_void_p), len(params), rows_mc,
+             rows.shape[1], layout.vis, n0, n1, scales_index, float(iso_weight), decay_index, float(decay),
+             betas[0], betas[1], eps, step, self._dev_step.data_ptr() if self.capturable else None,
+             vis_mc, stats_in.data_ptr(), stats_mc, rank, scratch.data_ptr(), stream())

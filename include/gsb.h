@@ -282,6 +282,24 @@ int gsb_map_update(const gsb_map_tensor* tensors_host, int n_tensors, const floa
                    int step, int32_t* step_dev, int32_t* vis_count_out, float* iso_loss_sum,
                    float* det_partials, void* stream);
 
+/* The same update as ONE kernel that is also the reduce-scatter before it and the all-gather after it, over
+ * NVLink multicast (NVLS; symmetric allocations mapped at a multicast address, e.g. torch symmetric memory):
+ * grad_rows_mc is the MULTICAST address of the gradient rows -- every load returns the sum over the GPUs,
+ * added inside the NVSwitch (multimem.ld_reduce) -- and the updated parameters of [n0, n1), the visibility
+ * counts (vis_count_mc, may be NULL) and this rank's loss scalars (stats_in[2] -> row `rank` of
+ * stats_mc[world][4] = total share, photometric share, isotropic sum, 0; may be NULL) are stored through the
+ * multicast addresses param_mc_host[k] / vis_count_mc / stats_mc into EVERY GPU's copy (multimem.st).
+ * tensors_host[k].param / exp_avg / exp_avg_sq are this GPU's own arrays (read for the update).  The caller
+ * puts a cross-GPU barrier before the launch (all rows written) and after it (all stores visible).  scratch:
+ * gsb_map_update_mc_scratch_floats(n0, n1) floats of this GPU, zeroed once.  The narrow tensors (width <= 4)
+ * must lie in the first 16 columns of a row (ops.RowLayout does). */
+size_t gsb_map_update_mc_scratch_floats(int64_t n0, int64_t n1);
+int gsb_map_update_mc(const gsb_map_tensor* tensors_host, const uint64_t* param_mc_host, int n_tensors,
+                      const float* grad_rows_mc, int64_t row_stride, int vis_col, int64_t n0, int64_t n1,
+                      int scales_tensor, float iso_weight, int decay_tensor, float decay, float beta1,
+                      float beta2, float eps, int step, int32_t* step_dev, int32_t* vis_count_mc,
+                      const float* stats_in, float* stats_mc, int rank, float* scratch, void* stream);
+
 /* ---- densify / prune surgery ------------------------------------------------
  * Replaces the per-tensor `value[keep_mask]` / `torch.cat` loops of gslam/pruning.py:10-53 and
  * gslam/insertion.py:27-62 over the 6 parameters and their 12 Adam states: every listed tensor

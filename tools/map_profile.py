@@ -37,3 +37,16 @@ for name, (calls, ms) in sorted(kt.items(), key=lambda kv: -kv[1][1] * kv[1][0])
     print(f"{name:24s} calls/step {calls / 5:4.1f}  {ms * 1e3:9.1f} us/call")
     tot += ms * calls / 5
 print(f"sum of C-ABI calls: {tot:.3f} ms/step")
+# the same step as ONE CUDA graph (what bench.py times): device ms per replay
+from gslam_b200.graph import GraphedStep
+gs = GraphedStep(lambda: step(g.viewmats, g.Ks, gt, exposure, sc.width, sc.height, n_views).total)
+for _ in range(3):
+    gs.replay()
+torch.cuda.synchronize()
+e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+e0.record()
+for _ in range(20):
+    gs.replay()
+e1.record()
+torch.cuda.synchronize()
+print(f"graph replay: {e0.elapsed_time(e1) / 20:.3f} ms per step ({gs.launches_per_replay} C-ABI launches)")
