@@ -49,9 +49,13 @@ def parse():
     ap.add_argument("--no-mapping", action="store_true")
     ap.add_argument("--map-eager", action="store_true")
     ap.add_argument("--map-comm", default="auto", choices=["auto", "nccl", "nvls"])
+    ap.add_argument("--map-big", default="auto", choices=["auto", "on", "off"],
+                    help="the cfg4 mapping leg (3M Gaussians, SH3, 1280x720, 16 views); auto: at 8 GPUs")
+    ap.add_argument("--big-gauss", type=int, default=3_000_000)
     ap.add_argument("--track-frames", type=int, default=12)
-    ap.add_argument("--slam-frames", type=int, default=60)
+    ap.add_argument("--slam-frames", type=int, default=300)
     ap.add_argument("--no-sequence", action="store_true")
+    ap.add_argument("--det", action="store_true", help="run every leg in deterministic accumulation mode")
     ap.add_argument("--no-f64", action="store_true", help="skip the float64 oracle run of the parity report")
     ap.add_argument("--no-cfg1", action="store_true", help="skip the 10k-Gaussian 320x240 leg (BASELINE configs[0])")
     return ap.parse_args()
@@ -331,6 +335,79 @@ def mapping_leg(args, dev, rank, world):
                     "all-gather of the parameters", "timed_loop": mode}
 
 
+def mapping_big_leg(args, dev, rank, world):
+    """BASELINE.json configs[3]: 3M Gaussians, SH degree 3 ([N,16,3] coefficients), 1280x720 OAK-D-shaped
+    frames, 16-keyframe window sharded over the ranks (2 views per GPU on 8), the same step as mapping_leg.
+    192 MB of parameters and 768 MB of gradient rows per rank: the first place the NVLink BANDWIDTH of the
+    reduce-scatter / all-gather shows, not its latency."""
+    import torch
+    import torch.distributed as dist
+    from gslam_b200.graph import GraphedStep
+    from gslam_b200.mapping import DEFAULT_LRS, PARAM_NAMES, FlatSplats, MappingStep, shard_views
+    from gslam_b200.optim import FusedAdam
+    from gslam_b200.synthetic import make_scene, target_images
+
+    n_views, n = 16, args.big_gauss
+    sc = make_scene(n, n_views, "oakd", 1.0)
+    mine = shard_views(n_views, rank, world)
+    tensors = [t.to(dev) for t in sc.params()]
+    gsh = torch.Generator().manual_seed(7)
+    sh = 0.1 * torch.randn(n, 16, 3, generator=gsh)
+    sh[:, 0] = sc.logit_colors * 0.5            # DC term from the logit colours
+    tensors[4] = sh.to(dev)
+    del sh
+    want_nvls = world > 1 and args.map_comm != "nccl"
+    splats = FlatSplats(tensors, align=4 * world, symmetric=dist.group.WORLD if want_nvls else None)
+    del tensors
+    opt = FusedAdam([dict(params=[p], lr=DEFAULT_LRS[nm]) for p, nm in zip(splats.params, PARAM_NAMES)],
+                    capturable=True)
+    mstep = MappingStep(splats, opt, comm=args.map_comm, sh_degree=3)
+    vm, K = sc.viewmats[mine].contiguous().to(dev), sc.Ks[mine].contiguous().to(dev)
+    gt = target_images(n_views, sc.height, sc.width)[mine].to(dev)
+    exposure = torch.zeros(len(mine), 2, device=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def eager():
+        return mstep(vm, K, gt, exposure, sc.width, sc.height, n_views).total
+
+    for _ in range(2):
+        eager()
+    barrier()
+    from gslam_b200 import ops
+    n_isects = int(ops.last_n_isects.item())
+    g_step = GraphedStep(eager)
+    for _ in range(2):
+        g_step.replay()
+    barrier()
+    steps = 5
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+    for e0, e1 in ev:
+        e0.record()
+        g_step.replay()
+        e1.record()
+    barrier()
+    g_step.check()
+    ms = sum(a.elapsed_time(b) for a, b in ev) / steps
+    t = torch.tensor([ms], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    res = {"metric": "mapping views/s (cfg4: 16-keyframe window, 3M Gaussians, SH3, 1280x720)",
+           "value": n_views * 1e3 / ms, "unit": "views/s", "ms_per_step": ms, "steps": steps, "n_views": n_views,
+           "n_gauss": n, "sh_degree": 3, "views_per_rank": len(mine), "n_ranks": world,
+           "n_isects_rank0": n_isects, "row_floats": 64, "gradient_rows_mb_per_rank": round(n * 64 * 4 / 1e6, 1),
+           "parameter_mb": round(n * 60 * 4 / 1e6, 1),
+           "comm": "none (one rank)" if world == 1 else ("nvls fused kernel" if mstep._nvls is not None else "nccl"),
+           "timed_loop": "CUDA-graph replay"}
+    del g_step, mstep, opt, splats
+    torch.cuda.empty_cache()
+    return res
+
+
 def tracking_closure_leg(args, dev):
     """The reference's own tracking iteration (gslam/frontend.py:604-662, the Adam phase of
     igs_track_lbfgs): the map is frozen (no_grad clone, gslam/backend.py:515), only the frame's pose
@@ -439,7 +516,7 @@ def tracking_frames_leg(args, dev):
             "timed_loop": "wall clock, host image in (pinned) -> pose out; graph replay per evaluation"}
 
 
-def slam_sequence_leg(args, dev, rgbd: bool):
+def slam_sequence_leg(args, dev, rgbd: bool, group="local"):
     """BASELINE cfg5: synthetic sequence through tracking + mapping + insertion / pruning
     (gslam_b200.slam, the inline equivalent of main.py), frames/s by wall clock.  rgbd=True is the
     reference's use_gt_depths mode: its poses are comparable with the ground truth (gauge fixed by
@@ -447,12 +524,15 @@ def slam_sequence_leg(args, dev, rgbd: bool):
     import torch
     from gslam_b200.slam import MapConfig, run_sequence
     F = args.slam_frames
-    slam, fps, gt = run_sequence(F, n_gauss=20_000, scale=1.0, device=dev, map_conf=MapConfig(use_gt_depths=rgbd))
+    # deterministic accumulation: the same sequence gives the same keyframes, map and trajectory in every run
+    slam, fps, gt = run_sequence(F, n_gauss=20_000, scale=1.0, device=dev,
+                                 map_conf=MapConfig(use_gt_depths=rgbd, deterministic=True), group=group)
     st = slam.stats
     est = torch.stack(slam.frame_poses)
     err = (est[:, :3, 3] - gt[:, :3, 3]).norm(dim=1)
     return {"metric": "sequence frames/s (tracking + mapping + insertion/pruning, 640x480)", "value": fps,
             "unit": "frames/s", "mode": "rgbd (use_gt_depths)" if rgbd else "monocular", "frames": F,
+            "deterministic": True, "mapping_ranks": slam.world,
             "keyframes": st.keyframes, "n_splats": st.n_splats,
             "mapping_iters": st.mapping_iters, "tracking_evals": st.tracking_evals,
             "pose_lbfgs_evals": st.pose_lbfgs_evals, "inserted": st.inserted, "pruned": st.pruned,
@@ -538,6 +618,7 @@ def run_ours(args):
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU fallback in the product path)"
+    ops.deterministic = bool(args.det)
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
@@ -748,8 +829,22 @@ def run_ours(args):
     mapping = None
     if not args.no_mapping:
         mapping = mapping_leg(args, dev, rank, world)
+    mapping_big = None
+    if args.map_big == "on" or (args.map_big == "auto" and world == 8 and not args.no_mapping):
+        try:
+            mapping_big = mapping_big_leg(args, dev, rank, world)
+        except Exception as e:   # noqa: BLE001  (reported in place; every rank fails or none: the step is collective)
+            import traceback as _tb
+            mapping_big = {"error": f"{type(e).__name__}: {e}", "where": _tb.format_exc().splitlines()[-8:]}
     closure = tracking_closure_leg(args, dev) if rank == 0 else None
     import traceback
+    seq_sharded = None
+    if world > 1 and not args.no_sequence:
+        # cfg5 with the mapping window sharded by view over ALL ranks (every rank runs the loop)
+        try:
+            seq_sharded = slam_sequence_leg(args, dev, True, group=None)
+        except Exception as e:   # noqa: BLE001
+            seq_sharded = {"error": f"{type(e).__name__}: {e}", "where": traceback.format_exc().splitlines()[-12:]}
     track_frames = slam_seq = None
     if rank == 0 and not args.no_sequence:
         # secondary legs: a failure here is reported in place and must not take the headline line down
@@ -855,9 +950,11 @@ def run_ours(args):
             "traffic_source": traffic_note,
             "roofline_stages": stages,
             "mapping": mapping,
+            "mapping_big": mapping_big,
             "tracking_closure": closure,
             "tracking_frames": track_frames,
             "sequence": slam_seq,
+            "sequence_sharded": seq_sharded,
         }
         parity_ok = True
         if world == 1 and not args.no_cpu_baseline:
@@ -881,6 +978,7 @@ def run_ours(args):
                                     "where": traceback.format_exc().splitlines()[-12:]}
                     parity_ok = False
         # the mapping object goes LAST so that a truncated tail of the line still carries it
+        line["mapping_big"] = line.pop("mapping_big")
         line["mapping"] = line.pop("mapping")
         print(json.dumps(line), flush=True)
         if not parity_ok:

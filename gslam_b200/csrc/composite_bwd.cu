@@ -280,9 +280,8 @@ composite_bwd_kernel(const float4* __restrict__ rec, const int32_t* __restrict__
 // units wrote for it -- its tile rectangle in row-major order, the units of a tile in order -- so the
 // gradient is a fixed-order sum, bit-identical from run to run.  The entry's position in a tile's
 // sorted list is found by a binary search for its depth bits (ties: scan for the flatten id; the
-// list is sorted by (depth bits, flatten id)).  Rectangles above TILES_DIRECT tiles are shared by
-// the warp, partial sums joined by a fixed butterfly.  v_rec is written for every (c, n), so the
-// caller need not zero it.
+// list is sorted by (depth bits, flatten id)).  v_rec is written for every (c, n), so the caller need
+// not zero it.
 // ---------------------------------------------------------------------------
 struct Row12 {
     float4 a, b, c;
@@ -321,15 +320,22 @@ __device__ __forceinline__ void gather_tile(Row12& acc, int lin, uint32_t dbits,
     }
 }
 
+// The (Gaussian, tile) pairs of a warp's 32 Gaussians are dealt to the lanes in flattened order, 32 per
+// round, so the dependent loads of the 32 searches overlap and a Gaussian that covers hundreds of tiles
+// costs more rounds, not one lane's serial walk (measured at 200 k Gaussians / 1.19 M intersections: the
+// one-lane-per-Gaussian form of this kernel took 250 us -- its slowest lane walked 48 tiles at ~7 us each).
+// A round's 32 rows go through shared memory; every owner then adds ITS rows of the round in pair order,
+// and the rounds are sequential, so each Gaussian's sum runs over its tiles in row-major order: fixed.
 __global__ void __launch_bounds__(256)
 composite_bwd_gather_kernel(const float* __restrict__ rec, const int32_t* __restrict__ radii, int64_t CN, int N,
                             int tile_w, int tile_h, const int32_t* __restrict__ offsets, int n_lin,
                             int64_t n_isects, const int64_t* __restrict__ isect_ids,
                             const int32_t* __restrict__ flatten_ids, const float4* __restrict__ det_rows,
                             const unsigned* __restrict__ det_mask, int64_t det_cap, float4* __restrict__ v_rec) {
+    __shared__ float4 s_rows[8][32][3];
     const unsigned full = 0xffffffffu;
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    const int lane = threadIdx.x & 31;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int r = (i < CN) ? radii[i] : 0;
     int x0 = 0, x1 = 0, y0 = 0, y1 = 0, cnt = 0, cam = 0;
     uint32_t dbits = 0;
@@ -341,38 +347,44 @@ composite_bwd_gather_kernel(const float* __restrict__ rec, const int32_t* __rest
         dbits = __float_as_uint(rec[i * GSB_REC + 9]);
     }
     const int n_tiles = tile_w * tile_h;
-    const int bw = x1 - x0;
+    const int bw = max(x1 - x0, 1);
+    int incl = cnt;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int y = __shfl_up_sync(full, incl, o);
+        if (lane >= o) incl += y;
+    }
+    const int excl = incl - cnt;
+    const int total = __shfl_sync(full, incl, 31);
     Row12 acc;
     acc.a = acc.b = acc.c = make_float4(0.f, 0.f, 0.f, 0.f);
-    const bool big = cnt > TILES_DIRECT;
-    if (!big) {
-        int tx = x0, ty = y0;
-        for (int t = 0; t < cnt; ++t) {
-            gather_tile(acc, cam * n_tiles + ty * tile_w + tx, dbits, (int)i, offsets, n_lin, n_isects, isect_ids,
-                        flatten_ids, det_rows, det_mask, det_cap);
-            if (++tx == x1) { tx = x0; ++ty; }
+    for (int base = 0; base < total; base += 32) {
+        const int p = base + lane;
+        // owner of pair p: the last lane whose first pair is <= p (zero-count lanes share their successor's start)
+        int owner = 0;
+#pragma unroll
+        for (int st = 16; st > 0; st >>= 1) {
+            const int cand = owner + st;
+            const int e = __shfl_sync(full, excl, cand & 31);
+            if (cand < 32 && e <= p) owner = cand;
         }
-    }
-    unsigned bigmask = __ballot_sync(full, big);
-    while (bigmask) {
-        const int src = __ffs(bigmask) - 1;
-        bigmask &= bigmask - 1;
-        const int o_x0 = __shfl_sync(full, x0, src), o_y0 = __shfl_sync(full, y0, src);
-        const int o_bw = max(__shfl_sync(full, bw, src), 1), o_cnt = __shfl_sync(full, cnt, src);
-        const int o_cam = __shfl_sync(full, cam, src);
-        const uint32_t o_d = __shfl_sync(full, dbits, src);
-        const int o_id = (int)__shfl_sync(full, (int)i, src);
+        const int t = p - __shfl_sync(full, excl, owner);
+        const int o_x0 = __shfl_sync(full, x0, owner), o_y0 = __shfl_sync(full, y0, owner);
+        const int o_bw = __shfl_sync(full, bw, owner), o_cam = __shfl_sync(full, cam, owner);
+        const uint32_t o_d = __shfl_sync(full, dbits, owner);
+        const int o_id = (int)__shfl_sync(full, (int)i, owner);
         Row12 part;
         part.a = part.b = part.c = make_float4(0.f, 0.f, 0.f, 0.f);
-        for (int t = lane; t < o_cnt; t += 32) {
+        if (p < total) {
             const int dy = t / o_bw;
             gather_tile(part, o_cam * n_tiles + (o_y0 + dy) * tile_w + o_x0 + (t - dy * o_bw), o_d, o_id, offsets,
                         n_lin, n_isects, isect_ids, flatten_ids, det_rows, det_mask, det_cap);
         }
-        float* pf = reinterpret_cast<float*>(&part);
-#pragma unroll
-        for (int k = 0; k < 12; ++k) pf[k] = warp_sum(pf[k]);       // fixed butterfly: same bits in every lane
-        if (lane == src) acc = part;
+        s_rows[warp][lane][0] = part.a; s_rows[warp][lane][1] = part.b; s_rows[warp][lane][2] = part.c;
+        __syncwarp();
+        const int qa = max(excl, base) - base, qb = min(excl + cnt, base + 32) - base;
+        for (int q = qa; q < qb; ++q) row_add(acc, s_rows[warp][q][0], s_rows[warp][q][1], s_rows[warp][q][2]);
+        __syncwarp();
     }
     if (i < CN) {
         float4* dst = v_rec + i * 3;

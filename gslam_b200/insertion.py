@@ -177,26 +177,34 @@ class InsertUsingImagePlaneGradients:
         self.grow_scale3d = grow_scale3d
 
     @torch.no_grad()
-    def masks(self, means2d_grad: Tensor, log_scales: Tensor, width: int, height: int, n_cameras: int):
-        """(to_duplicate, to_split) [N] from means2d.grad [C,N,2]."""
+    def masks(self, means2d_grad: Tensor, log_scales: Tensor, width: int, height: int, n_cameras: int, group=None):
+        """(to_duplicate, to_split) [N] from means2d.grad [C,N,2].  In a view-sharded step means2d_grad holds
+        this rank's views and n_cameras is the window's total: the per-Gaussian sum of the gradient norms is
+        all-reduced over `group`, so every rank derives the same masks."""
+        from .mapping import allreduce_sum_
         g = means2d_grad * means2d_grad.new_tensor([width / 2.0 * n_cameras, height / 2.0 * n_cameras])
-        high = g.norm(dim=-1).mean(dim=0) > self.grow_grad2d
+        high = allreduce_sum_(g.norm(dim=-1).sum(dim=0).contiguous(), group) / max(n_cameras, 1) > self.grow_grad2d
         small = torch.exp(log_scales).max(dim=-1).values <= self.grow_scale3d
         return high & small, high & ~small
 
     @torch.no_grad()
     def step(self, splats: FlatSplats, optimizer, rasterization_output: RasterizationOutput,
-             generator: Optional[torch.Generator] = None):
+             generator: Optional[torch.Generator] = None, group="local", n_views_total: Optional[int] = None):
         """Returns (num_duplicate, num_split); `rasterization_output.means2d.grad` must be populated
-        (`out.means2d.retain_grad()` before backward, gslam/backend.py:326)."""
+        (`out.means2d.retain_grad()` before backward, gslam/backend.py:326).  group / n_views_total: the
+        view-sharded step (a rank without a view passes an output whose means2d is None)."""
         from .rasterization import quat_scale_to_covar_preci
         from .mapping import PARAM_NAMES
         out = rasterization_output
-        grad = out.means2d.grad
-        if grad is None:
-            raise RuntimeError("InsertUsingImagePlaneGradients: means2d.grad is empty (call retain_grad())")
         P = {name: p.detach() for name, p in zip(PARAM_NAMES, splats.params)}
-        dup, split = self.masks(grad, P["scales"], out.width, out.height, out.n_cameras)
+        if out.means2d is None:
+            grad = P["means"].new_zeros(0, splats.n, 2)
+        else:
+            grad = out.means2d.grad
+            if grad is None:
+                raise RuntimeError("InsertUsingImagePlaneGradients: means2d.grad is empty (call retain_grad())")
+        n_cam = out.n_cameras if n_views_total is None else n_views_total
+        dup, split = self.masks(grad, P["scales"], out.width, out.height, n_cam, group)
         both = torch.cat([torch.nonzero(dup).reshape(-1), torch.nonzero(split).reshape(-1)])
         n_dup = int(dup.sum().item())                      # the reference reads both counts too (:318-319)
         n_split = both.numel() - n_dup

@@ -78,7 +78,7 @@ def fused_ssim(img1: Tensor, img2: Tensor, padding: str = "same", train: bool = 
 
 class _PhotometricSSIM(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, render, gt, exposure, ssim_weight, mode, unit_upstream=False, det=False):
+    def forward(ctx, render, gt, exposure, ssim_weight, mode, unit_upstream=False, det=False, scale=1.0):
         ctx.set_materialize_grads(False)
         # render [C,H,W,5] = (r, g, b, depth, beta); gt [C,H,W,3]; exposure [C,2] or None
         assert render.is_cuda and render.is_contiguous() and render.shape[-1] == 5
@@ -92,7 +92,9 @@ class _PhotometricSSIM(torch.autograd.Function):
         need_exp = exposure is not None and ctx.needs_input_grad[2]
         v_exp = torch.zeros(C, 2, dtype=torch.float32, device=dev) if need_exp else None
         part = ops.det_scratch(lib().gsb_photo_loss_det_floats(C, H, W), dev) if det else None
-        call("gsb_photo_loss", ptr(render), ptr(gt), ptr(exposure_c), mode, C, H, W, 1.0 - ssim_weight,
+        # `scale` (a view-sharded step's share of the window) is folded into every coefficient: the value and
+        # the gradient written here are already scaled, so no extra pass multiplies v_render later
+        call("gsb_photo_loss", ptr(render), ptr(gt), ptr(exposure_c), mode, C, H, W, (1.0 - ssim_weight) * scale,
              ptr(loss_sum), ptr(loss_out), ptr(v_render), ptr(v_exp), ptr(part), stream())
         total, photo = loss_out[0], loss_out[1]
         ssim = None
@@ -107,9 +109,9 @@ class _PhotometricSSIM(torch.autograd.Function):
                  ptr(ssim_sum), ptr(maps[0]), ptr(maps[1]), ptr(maps[2]), ptr(spart), stream())
             ctx.count = C * 3 * (H - 10) * (W - 10)
             # total + w * (1 - ssim_sum / count) in two launches
-            total = torch.sub(total, ssim_sum[0], alpha=ssim_weight / ctx.count) + ssim_weight
+            total = torch.sub(total, ssim_sum[0], alpha=scale * ssim_weight / ctx.count) + scale * ssim_weight
         ctx.save_for_backward(render, gt, maps, v_render, v_exp)
-        ctx.ssim_weight = ssim_weight
+        ctx.ssim_weight = ssim_weight * scale
         ctx.unit_upstream = bool(unit_upstream) and ssim_weight == 0.0
         ctx.mark_non_differentiable(photo)
         return total, photo
@@ -121,7 +123,7 @@ class _PhotometricSSIM(torch.autograd.Function):
         g = g.contiguous()
         if ctx.unit_upstream:
             # the caller calls backward() on this loss itself: the incoming gradient is exactly 1
-            return v_render, None, v_exp, None, None, None, None
+            return v_render, None, v_exp, None, None, None, None, None
         call("gsb_scale_by_scalar", ptr(v_render), v_render.numel(), ptr(g), stream())
         if maps is not None:
             img1 = render[..., :3].permute(0, 3, 1, 2)
@@ -130,18 +132,18 @@ class _PhotometricSSIM(torch.autograd.Function):
             call("gsb_ssim_bwd", ptr(img1), ptr(img2), _strides(img1), _strides(img2), C, 3, H, W,
                  ptr(maps[0]), ptr(maps[1]), ptr(maps[2]), ptr(g), -ctx.ssim_weight / ctx.count, ptr(v1),
                  _strides(v1), 1, stream())
-        return v_render, None, (v_exp * g if v_exp is not None else None), None, None, None, None
+        return v_render, None, (v_exp * g if v_exp is not None else None), None, None, None, None, None
 
 
 def photometric_ssim_loss(render: Tensor, gt: Tensor, exposure: Optional[Tensor] = None,
                           ssim_weight: float = 0.2, mode: str = "mapping",
-                          deterministic: Optional[bool] = None):
+                          deterministic: Optional[bool] = None, scale: float = 1.0):
     """(1 - w) * photometric + w * (1 - SSIM_valid)  ->  (total, photometric value).
 
     `render` is the [C,H,W,5] tensor behind RasterizationOutput (rgbs/depthmaps/betas are
     views of it; rasterization() attaches it as ``out.render``)."""
     det = ops.deterministic if deterministic is None else bool(deterministic)
-    return _PhotometricSSIM.apply(render, gt, exposure, float(ssim_weight), PHOTO_MODES[mode], False, det)
+    return _PhotometricSSIM.apply(render, gt, exposure, float(ssim_weight), PHOTO_MODES[mode], False, det, float(scale))
 
 
 def tracking_loss(render: Tensor, gt: Tensor, exposure: Optional[Tensor] = None,

@@ -227,6 +227,7 @@ class MappingStep:
         are symmetric and multicast is there, else nccl."""
         if render_fn is None:
             from .rasterization import rasterization as render_fn
+        self._fused_loss = loss_fn is None
         if loss_fn is None:
             from .losses import photometric_ssim_loss as loss_fn
         self.splats, self.opt = splats, optimizer
@@ -293,43 +294,65 @@ class MappingStep:
         bg = background if background is not None else torch.zeros(c_local, 3, device=viewmats.device)
         kw = {} if self.sh_degree is None else {"sh_degree": self.sh_degree}
         self._mark("begin")
-        out = self.render_fn(P[0], P[1], P[2], P[3], P[4], viewmats, Ks, width, height, packed=False,
-                             render_mode="RGB+D", log_uncertainties=P[5], backgrounds=bg, **kw)
-        # the image losses are means over ALL views of the window: weight this rank's share
-        total, photo = self.loss_fn(out.render, gt_imgs, exposure, self.ssim_weight, "mapping")
-        share = c_local / float(n_views_total)
-        loss = total * share
-        if self.tv_w:
-            # a sum (not a mean) over this rank's views: no share factor (gslam/backend.py:297-318)
-            loss = loss + self.tv_w * edge_aware_tv(out.depthmaps, out.rgbs, out.alphas[..., 0] > 0.4)
-        if gt_depths is not None:
-            # use_gt_depths (gslam/backend.py:320-323): 0.1 * mean |depth - gt| over gt > 0, a mean over
-            # the window's valid pixels: this rank's share is its valid-pixel fraction of the window total
-            valid = (gt_depths > 0).to(out.depthmaps.dtype)
-            n_valid = allreduce_sum_(valid.sum().view(1).clone(), self.group).clamp_min(1.0)
-            loss = loss + 0.1 * ((out.depthmaps - gt_depths).abs() * valid).sum() / n_valid[0]
-        if self.retain_means2d_grad:
-            out.means2d.retain_grad()
-        kernels_write_rows = self.collect_grads is None
-        if kernels_write_rows:
-            ops.grad_rows_out, ops.grad_rows_written = rows, False
-        try:
-            loss.backward()
-        finally:
-            ops.grad_rows_out = None
-        if kernels_write_rows:
-            if not ops.grad_rows_written:
-                raise RuntimeError("MappingStep: the backward pass did not write the gradient rows "
-                                   "(render_fn is not the CUDA rasterizer? pass collect_grads)")
+        if c_local == 0:
+            # more ranks than views in the window (the first keyframes of a sequence): this rank renders
+            # nothing, contributes zero rows and still takes part in every collective
+            from types import SimpleNamespace
+            dev = sp.flat.device
+            rows[:sp.n].zero_()
+            zero = torch.zeros((), device=dev)
+            total_share, photo, share = zero, zero, 0.0
+            if gt_depths is not None:           # the window's valid-pixel count is a collective: take part
+                allreduce_sum_(torch.zeros(1, device=dev), self.group)
+            out = SimpleNamespace(radii=torch.zeros(0, sp.n, dtype=torch.int32, device=dev),
+                                  n_touched=torch.zeros(0, sp.n, dtype=torch.int64, device=dev),
+                                  depthmaps=torch.zeros(0, height, width, device=dev), means2d=None,
+                                  width=width, height=height, n_cameras=0)
         else:
-            self.collect_grads(P, out.radii, rows, lay)
+            out = self.render_fn(P[0], P[1], P[2], P[3], P[4], viewmats, Ks, width, height, packed=False,
+                                 render_mode="RGB+D", log_uncertainties=P[5], backgrounds=bg, **kw)
+            # the image losses are means over ALL views of the window: weight this rank's share
+            share = c_local / float(n_views_total)
+            if self._fused_loss:
+                # the share is folded into the loss kernel's coefficients: `loss` is already this rank's part and
+                # its gradient needs no scaling pass (photo stays the plain photometric value)
+                loss, photo = self.loss_fn(out.render, gt_imgs, exposure, self.ssim_weight, "mapping", scale=share)
+                total_share = loss.detach()
+            else:
+                total, photo = self.loss_fn(out.render, gt_imgs, exposure, self.ssim_weight, "mapping")
+                loss = total * share
+                total_share = total.detach() * share
+            if self.tv_w:
+                # a sum (not a mean) over this rank's views: no share factor (gslam/backend.py:297-318)
+                loss = loss + self.tv_w * edge_aware_tv(out.depthmaps, out.rgbs, out.alphas[..., 0] > 0.4)
+            if gt_depths is not None:
+                # use_gt_depths (gslam/backend.py:320-323): 0.1 * mean |depth - gt| over gt > 0, a mean over
+                # the window's valid pixels: this rank's share is its valid-pixel fraction of the window total
+                valid = (gt_depths > 0).to(out.depthmaps.dtype)
+                n_valid = allreduce_sum_(valid.sum().view(1).clone(), self.group).clamp_min(1.0)
+                loss = loss + 0.1 * ((out.depthmaps - gt_depths).abs() * valid).sum() / n_valid[0]
+            if self.retain_means2d_grad:
+                out.means2d.retain_grad()
+            kernels_write_rows = self.collect_grads is None
+            if kernels_write_rows:
+                ops.grad_rows_out, ops.grad_rows_written = rows, False
+            try:
+                loss.backward()
+            finally:
+                ops.grad_rows_out = None
+            if kernels_write_rows:
+                if not ops.grad_rows_written:
+                    raise RuntimeError("MappingStep: the backward pass did not write the gradient rows "
+                                       "(render_fn is not the CUDA rasterizer? pass collect_grads)")
+            else:
+                self.collect_grads(P, out.radii, rows, lay)
         self._mark("backward_done")
 
         n = sp.n
         per = sp.cap // world
         n0 = min(rank * per, n)
         n1 = min(n0 + per, n) if rank * per < n else n0
-        mine = torch.stack([total.detach() * share, photo.detach() * share])
+        mine = torch.stack([total_share, photo.detach() * share])
         if not step_optimizer:
             # densification decides from the whole reduced gradient on every rank and the parameters it
             # re-creates take no step: all-reduce, no update (apply_pending() runs it if nothing changed)

@@ -39,7 +39,7 @@ from .losses import photometric_ssim_loss
 from .graph import GraphedStep, shared_pool
 from .insertion import InsertFromDepthMap, InsertUsingImagePlaneGradients, KeyframeView
 from .map import GaussianSplattingData
-from .mapping import DEFAULT_LRS, LOCAL, PARAM_NAMES, FlatSplats, MappingStep
+from .mapping import DEFAULT_LRS, LOCAL, PARAM_NAMES, FlatSplats, MappingStep, _world, allreduce_sum_
 from .optim import FusedAdam
 from .primitives import Camera, PoseZhou, pose_batch
 from .pruning import prune_round
@@ -134,8 +134,17 @@ class SlamStats:
 
 class Slam:
     def __init__(self, camera: Camera, map_conf: Optional[MapConfig] = None,
-                 track_conf: Optional[TrackingConfig] = None, device="cuda", seed: int = 0):
+                 track_conf: Optional[TrackingConfig] = None, device="cuda", seed: int = 0, group=LOCAL):
+        """group: LOCAL (default) maps on this GPU alone.  A process group (None = WORLD) shards the MAPPING
+        window by view over its ranks (mapping.MappingStep): every rank runs this same loop on the same
+        frames -- tracking, keyframe decisions, insertion and the window-pose L-BFGS are replicated, the
+        mapping iterations are sharded -- which needs MapConfig(deterministic=True), so that the replicated
+        arithmetic is bit-identical and every rank takes the same decisions (and issues the same collectives)."""
         self.conf = map_conf or MapConfig()
+        self.group = group
+        self.rank, self.world = _world(group)
+        if self.world > 1 and not self.conf.deterministic:
+            raise ValueError("a view-sharded Slam needs MapConfig(deterministic=True)")
         self.camera = camera.to(device)
         self.dev = torch.device(device)
         if self.dev.type != "cuda":
@@ -156,7 +165,7 @@ class Slam:
         self.total_step = 0
         self.stats = SlamStats()
         empty = [torch.zeros((0, w) if w > 1 else (0,), device=self.dev) for w in (3, 4, 3, 1, 3, 1)]
-        self.splats = FlatSplats(empty)
+        self.splats = FlatSplats(empty, align=self.world)
         # one optimizer, one group per parameter: the reference's six Adam instances (:565-590)
         self.opt = FusedAdam([{"params": [p], "lr": DEFAULT_LRS[name]}
                               for p, name in zip(self.splats.params, PARAM_NAMES)], capturable=True)
@@ -164,7 +173,7 @@ class Slam:
         self.step = MappingStep(self.splats, self.opt, ssim_weight=c.ssim_weight,
                                 isotropic_weight=c.isotropic_regularization_weight,
                                 opacity_decay=c.opacity_decay,
-                                group=LOCAL)       # one process tracks and maps: no collective, whatever the job size
+                                group=group, comm="nccl")    # LOCAL: no collective, whatever the job size
         self.bg1 = torch.zeros(1, 3, device=self.dev)
 
     # ---- rendering helpers ----------------------------------------------------------------------
@@ -176,6 +185,9 @@ class Slam:
         return rasterization(P[0], P[1], P[2], P[3], P[4], viewmats.contiguous(), Ks, self.camera.width,
                              self.camera.height, packed=False, render_mode="RGB+D", log_uncertainties=P[5],
                              backgrounds=self.bg1.expand(C, 3).contiguous())
+
+    def _pose_batch(self, poses) -> Tensor:
+        return pose_batch(poses) if poses else torch.zeros(0, 4, 4, device=self.dev)
 
     def _views(self) -> List[KeyframeView]:
         with torch.no_grad():
@@ -246,20 +258,22 @@ class Slam:
             p.dR.grad = None
             p.dt.grad = None
         self.step.retain_means2d_grad = densify
-        res = self.step(pose_batch(w.poses), w.Ks, w.gt, w.exposure, self.camera.width, self.camera.height,
-                        len(w.poses), step_optimizer=not densify, gt_depths=w.gt_depths)
+        res = self.step(self._pose_batch(w.poses), w.Ks, w.gt, w.exposure, self.camera.width, self.camera.height,
+                        self._n_window, step_optimizer=not densify, gt_depths=w.gt_depths)
         changed = False
         if densify:
             # the reference densifies between backward and the optimizer step (:328-351): the
             # parameters it re-creates carry no gradient, so that iteration takes no splat step and
             # only the opacity decay applies (radii padded with zeros for the new rows)
-            n_dup, n_split = self.insertion_3dgs.step(self.splats, self.opt, res.outputs, self.gen)
+            n_dup, n_split = self.insertion_3dgs.step(self.splats, self.opt, res.outputs, self.gen,
+                                                      group=self.group, n_views_total=self._n_window)
             self.stats.inserted += n_dup + n_split
             self.stats.densified += n_dup + n_split
             changed = n_dup + n_split > 0
             if changed:
                 with torch.no_grad():
-                    seen_twice = (res.outputs.radii > 0).sum(dim=0) > 1
+                    seen_twice = torch.cat([res.vis_count > 1,          # reduced over the window's views (all ranks)
+                                            res.vis_count.new_zeros(n_dup + n_split, dtype=torch.bool)])
                     self.splats.params[3].mul_(torch.where(seen_twice, c.opacity_decay, 1.0))
                     res.radii = res.outputs.radii
                     res.n_touched = torch.cat([res.n_touched, res.n_touched.new_zeros(
@@ -295,15 +309,16 @@ class Slam:
                 p.dR.grad = None
                 p.dt.grad = None
             self.step.retain_means2d_grad = False
-            res = self.step(pose_batch(w.poses), w.Ks, w.gt, w.exposure, self.camera.width, self.camera.height,
-                            len(w.poses), gt_depths=w.gt_depths)
+            res = self.step(self._pose_batch(w.poses), w.Ks, w.gt, w.exposure, self.camera.width, self.camera.height,
+                            self._n_window, gt_depths=w.gt_depths)
             with torch.no_grad():
                 ring.index_copy_(0, pos.view(1) % ring.shape[0], res.photometric.detach().view(1))
                 pos.add_(1)
             box["res"] = self._light(res)
             return box["res"].total
 
-        g = GraphedStep(fn, headroom=1.5, n_isects_hint=int(ops.last_n_isects.item()), pool=shared_pool(self.dev))
+        hint = int(ops.last_n_isects.item()) if (w.poses and ops.last_n_isects is not None) else 1
+        g = GraphedStep(fn, headroom=1.5, n_isects_hint=hint, pool=shared_pool(self.dev))
         grads = [(q, q.grad) for p in w.poses for q in (p.dR, p.dt)]
         return _MappingGraph(g, box["res"], ring, pos, grads)
 
@@ -320,11 +335,19 @@ class Slam:
         n_iters = c.num_iters_mapping if n_iters is None else n_iters
         stopper = StopOnPlateau(3, 0.012)
         self.step.tv_w = c.depth_regularization_weight if regularize else 0.0
-        window = self.optimization_window()
-        w = _Window([k.pose for k in window], torch.stack([k.img for k in window]),
-                    torch.stack([k.exposure for k in window]),
+        window_all = self.optimization_window()
+        # a view belongs to the rank given by its keyframe's position in the (append-only) keyframe list, so
+        # its owner -- and the Adam state of its pose -- never changes while the window slides
+        pos = {k: i for i, k in enumerate(sorted(self.keyframes))}
+        window = [k for k in window_all if pos[k.index] % self.world == self.rank]
+        self._n_window = len(window_all)
+        H, W = self.camera.height, self.camera.width
+        w = _Window([k.pose for k in window],
+                    torch.stack([k.img for k in window]) if window else torch.zeros(0, H, W, 3, device=self.dev),
+                    torch.stack([k.exposure for k in window]) if window else torch.zeros(0, 2, device=self.dev),
                     self.camera.intrinsics.expand(len(window), 3, 3).contiguous(),
-                    torch.stack([k.gt_depth for k in window]) if c.use_gt_depths else None)
+                    (torch.stack([k.gt_depth for k in window]) if window else torch.zeros(0, H, W, device=self.dev))
+                    if c.use_gt_depths else None)
         for k in self.keyframes.values():            # pose_optimizer.zero_grad() (:265): nothing stale steps
             k.pose.dR.grad = None
             k.pose.dt.grad = None
@@ -390,12 +413,36 @@ class Slam:
         with torch.no_grad():
             for k, dmap in zip(window, res.outputs.depthmaps):
                 k.est_depths = dmap.detach().clone()
+            if self.world > 1:
+                self._share_window(window_all, pos)
             if prune:
                 self.stats.pruned += prune_round(
                     self.splats, self.opt, res.radii, res.n_touched, c.opacity_pruning_threshold,
                     c.size_pruning_threshold, 3 if c.enable_visibility_pruning else None,
-                    c.optim_window_last_n_keyframes)
+                    c.optim_window_last_n_keyframes, group=self.group,
+                    n_views_total=len(window_all) if self.world > 1 else None)
         self.stats.n_splats = self.splats.n
+
+    @torch.no_grad()
+    def _share_window(self, window_all, pos) -> None:
+        """End of a sharded round: every rank gets the poses and the estimated depth maps of the views the
+        other ranks optimised (9 floats per view + one depth map per view, one all-reduce each:
+        the owner contributes the value, everybody else zeros)."""
+        H, W = self.camera.height, self.camera.width
+        poses = torch.zeros(len(window_all), 9, device=self.dev)
+        depths = torch.zeros(len(window_all), H, W, device=self.dev)
+        for i, k in enumerate(window_all):
+            if pos[k.index] % self.world == self.rank:
+                poses[i, :6], poses[i, 6:] = k.pose.dR.detach(), k.pose.dt.detach()
+                if k.est_depths is not None:
+                    depths[i] = k.est_depths
+        allreduce_sum_(poses, self.group)
+        allreduce_sum_(depths, self.group)
+        for i, k in enumerate(window_all):
+            if pos[k.index] % self.world != self.rank:
+                k.pose.dR.copy_(poses[i, :6])
+                k.pose.dt.copy_(poses[i, 6:])
+                k.est_depths = depths[i].clone()
 
     @torch.no_grad()
     def run_pruning(self) -> None:
@@ -406,7 +453,7 @@ class Slam:
         c = self.conf
         self.stats.pruned += prune_round(self.splats, self.opt, out.radii, out.n_touched,
                                          c.opacity_pruning_threshold, c.size_pruning_threshold, None,
-                                         c.optim_window_last_n_keyframes)
+                                         c.optim_window_last_n_keyframes, group=LOCAL)   # replicated: no collective
         self.stats.n_splats = self.splats.n
 
     def optimize_poses_lbfgs(self) -> Optional[float]:
@@ -580,10 +627,10 @@ def synthetic_sequence(n_frames: int, n_gauss: int = 20000, scale: float = 1.0, 
 
 def run_sequence(n_frames: int, n_gauss: int = 20000, scale: float = 1.0, device="cuda", seed: int = 0,
                  map_conf: Optional[MapConfig] = None, track_conf: Optional[TrackingConfig] = None,
-                 idle_rounds: int = 1):
-    """cfg5: the whole loop over a synthetic sequence -> (Slam, frames/s, gt viewmats)."""
+                 idle_rounds: int = 1, group=LOCAL):
+    """cfg5: the whole loop over a synthetic sequence -> (Slam, frames/s, gt viewmats).  `group`: see Slam."""
     cam, imgs, gt_poses, depths = synthetic_sequence(n_frames, n_gauss, scale, device, seed)
-    slam = Slam(cam, map_conf, track_conf, device, seed)
+    slam = Slam(cam, map_conf, track_conf, device, seed, group=group)
     torch.cuda.synchronize()
     t0 = time.perf_counter()
     for i in range(n_frames):
