@@ -58,6 +58,9 @@ SIGNATURES = {
     "gsb_vis_count": (_i, [_p, _i, _l, _p, _p]),
     "gsb_isotropic_reg": (_i, [_p, _p, _l, _f, _p, _p, _p, _p]),
     "gsb_rows_resize": (_i, [_p, _i, _l, _p, _l, _l, _p]),
+    "gsb_lbfgs_state_bytes": (_z, []),
+    "gsb_lbfgs_init": (_i, [_p, _p, _i, _i, _i, _i, ct.c_double, ct.c_double, ct.c_double, _p]),
+    "gsb_lbfgs_advance": (_i, [_p, _p, _p, _p, _p]),
     "gsb_pose_fwd": (_i, [_p, _p, _p, _i, _p, _p]),
     "gsb_pose_bwd": (_i, [_p, _p, _p, _i, _p, _p, _p]),
 }

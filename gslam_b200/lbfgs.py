@@ -201,3 +201,33 @@ def lbfgs_minimize(evaluate: Evaluate, x0: np.ndarray, lr: float = 1.0, max_iter
         if abs(loss - prev_loss) < tolerance_change:
             break
     return LbfgsResult(x, first, last[0], evals, n_iter)
+
+
+class DeviceLbfgs:
+    """The same optimizer as `lbfgs_minimize`, resident on the GPU (csrc/lbfgs.cu): `reset(theta)` starts a
+    minimisation from the device vector `theta`; after every evaluation of the objective at `theta` (loss and
+    gradient in `result[1 + n]`, float32) `advance(theta, result)` writes the next point to evaluate into
+    `theta`.  Nothing here synchronises: the caller replays evaluate + advance `max_eval` times (one CUDA
+    graph) and reads `summary` (finished, evaluations used, iterations, first loss, last loss) once."""
+
+    def __init__(self, n: int, device, lr: float = 1.0, max_iter: int = 20, max_eval: Optional[int] = None,
+                 tolerance_grad: float = 1e-7, tolerance_change: float = 1e-9, history_size: int = 100):
+        import torch
+        from ._lib import lib
+        self.n, self.lr, self.max_iter = int(n), float(lr), int(max_iter)
+        self.max_eval = int(max_eval) if max_eval is not None else max_iter * 5 // 4
+        self.tol_grad, self.tol_change = float(tolerance_grad), float(tolerance_change)
+        self.hist = min(int(history_size), 16)
+        if n > 96:
+            raise ValueError("DeviceLbfgs holds at most 96 unknowns")
+        self.state = torch.zeros(lib().gsb_lbfgs_state_bytes(), dtype=torch.uint8, device=device)
+        self.summary = torch.zeros(5, dtype=torch.float32, device=device)
+
+    def reset(self, theta) -> None:
+        from ._lib import call, ptr, stream
+        call("gsb_lbfgs_init", ptr(self.state), ptr(theta), self.n, self.hist, self.max_iter, self.max_eval, self.lr,
+             self.tol_grad, self.tol_change, stream())
+
+    def advance(self, theta, result) -> None:
+        from ._lib import call, ptr, stream
+        call("gsb_lbfgs_advance", ptr(self.state), ptr(theta), ptr(result), ptr(self.summary), stream())

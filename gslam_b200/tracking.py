@@ -41,7 +41,7 @@ from torch import Tensor
 
 from . import ops
 from .graph import GraphedStep
-from .lbfgs import lbfgs_minimize
+from .lbfgs import DeviceLbfgs, lbfgs_minimize
 from .losses import tracking_loss
 from .map import GaussianSplattingData
 from .primitives import Camera, pose_chain, affine_inverse  # noqa: F401  (re-exported)
@@ -64,6 +64,8 @@ class TrackingConfig:
     lbfgs_max_iter: int = 20                   # torch.optim.LBFGS default (max_eval = 25); 0 skips the phase
     lbfgs_tolerance_change: float = 1e-9
     exposure_lr: float = 0.01                  # SGD param-group lr of the exposure (:204-209)
+    lbfgs_on_device: bool = True               # the L-BFGS state machine runs on the GPU (csrc/lbfgs.cu): one sync per
+                                               # frame; False: gslam_b200.lbfgs on the host, one sync per evaluation
     deterministic: bool = False                # fixed-order gradient accumulation (ops.deterministic): the same
                                                # frame gives bit-identical poses from run to run
 
@@ -158,6 +160,11 @@ class Tracker:
         self.headroom = 1.5          # capacity of the captured key buffers over the measured count
         self.n_evals = 0
         self.n_syncs = 0
+        c = self.conf
+        self.dev_lbfgs = DeviceLbfgs(N_THETA, d, lr=c.pose_optim_lr, max_iter=max(c.lbfgs_max_iter, 1),
+                                     tolerance_change=c.lbfgs_tolerance_change, history_size=c.lbfgs_history)
+        self.summary_host = torch.zeros(5 + N_THETA).pin_memory()
+        self.lbfgs_evals_used = 0
 
     # ---- the map -------------------------------------------------------------------------------
     def set_map(self, splats: GaussianSplattingData) -> None:
@@ -222,6 +229,13 @@ class Tracker:
         self.result_host.copy_(self.result, non_blocking=True)
         return loss
 
+    def _step_closure_dev(self) -> Tensor:
+        """L-BFGS evaluation with the optimizer on the device: evaluate at theta, let the state machine
+        consume (loss, gradient) and write the next trial point into theta.  No transfer, no sync."""
+        loss = self._evaluate()
+        self.dev_lbfgs.advance(self.theta, self.result)
+        return loss
+
     def _step_adam(self) -> Tensor:
         """torch.optim.Adam(params, lr) defaults (betas .9/.999, eps 1e-8) on the 11 unknowns."""
         loss = self._evaluate()
@@ -253,7 +267,8 @@ class Tracker:
     def _graph(self, kind: str) -> GraphedStep:
         g = self._graphs.get(kind)
         if g is None:
-            fn = {"closure": self._step_closure, "adam": self._step_adam, "sgd": self._step_sgd}[kind]
+            fn = {"closure": self._step_closure, "closure_dev": self._step_closure_dev, "adam": self._step_adam,
+                  "sgd": self._step_sgd}[kind]
             saved = [t.clone() for t in (self.theta.detach(), self.m, self.v, self.step_no, self.lr_scale,
                                          self.ring_pos)]
             with ops.deterministic_mode(self.conf.deterministic):     # baked into the captured kernels
@@ -312,6 +327,8 @@ class Tracker:
             loss = self._losses(c.n_adam_iters)[-1] if c.n_adam_iters else float("nan")
             adam.check() if c.n_adam_iters else None
             return self._finish(loss)
+        if c.lbfgs_on_device:
+            return self._lbfgs_on_device(adam if c.n_adam_iters else None)
         closure_graph = self._graph("closure")
         self.theta_host.copy_(self.theta.detach())            # syncs: the Adam phase is done
         self.n_syncs += 1
@@ -336,6 +353,27 @@ class Tracker:
         with torch.no_grad():
             self.theta.copy_(self.theta_host)
         return self._finish(last[0])
+
+    def _lbfgs_on_device(self, adam: Optional[GraphedStep]) -> TrackResult:
+        """The L-BFGS phase with the optimizer on the GPU: max_eval replays of (evaluate, advance) queued back
+        to back, ONE read-back at the end (the reference syncs inside every line-search comparison)."""
+        g = self._graph("closure_dev")        # (its capture warm-up moved theta and the optimizer state: reset after)
+        self.dev_lbfgs.reset(self.theta)
+        # a search may spend one evaluation more than the budget left (its first trial is not counted against
+        # max_ls, as in torch): max_eval + 1 bounds the whole minimisation
+        n = self.dev_lbfgs.max_eval + 1
+        for _ in range(n):
+            g.replay()
+        self.n_evals += n
+        with torch.no_grad():
+            self.summary_host.copy_(torch.cat([self.dev_lbfgs.summary, self.theta.detach()]), non_blocking=True)
+        torch.cuda.current_stream(self.dev).synchronize()
+        self.n_syncs += 1
+        if adam is not None:
+            adam.check()
+        g.check()
+        self.lbfgs_evals_used = int(self.summary_host[1])
+        return self._finish(float(self.summary_host[4]))
 
     def _track_sgd(self, img: Tensor, init_viewmat: Tensor, exposure_init: Optional[Tensor] = None,
                   gt_depth: Optional[Tensor] = None, n_iters: Optional[int] = None,

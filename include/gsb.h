@@ -325,6 +325,19 @@ int gsb_pose_fwd(const float* Rt, const float* dR, const float* dt, int C, float
 int gsb_pose_bwd(const float* Rt, const float* dR, const float* v_viewmats, int C, float* v_dR,
                  float* v_dt, void* stream);
 
+/* ---- L-BFGS with a strong-Wolfe search as a device-side state machine ------------
+ * The optimizer of gslam/frontend.py:604-662 / gslam/backend.py:436-506 (torch.optim.LBFGS, strong_wolfe)
+ * with its whole state in `state` (gsb_lbfgs_state_bytes() bytes of device memory).  gsb_lbfgs_init starts
+ * a minimisation from theta[n] (n <= 96, history_size <= 16; max_eval = torch's default max_iter * 5 / 4).
+ * Then repeat max_eval times, without any host sync: evaluate the objective at theta -> result[1 + n] =
+ * (loss, gradient); gsb_lbfgs_advance consumes it and writes the next point to evaluate into theta.  Once
+ * the search has finished theta holds the final iterate and further calls change nothing.  summary[5]
+ * (may be NULL) = (finished, evaluations used, iterations, first loss, loss of the last evaluation). */
+size_t gsb_lbfgs_state_bytes(void);
+int gsb_lbfgs_init(void* state, const float* theta, int n, int history_size, int max_iter, int max_eval,
+                   double lr, double tolerance_grad, double tolerance_change, void* stream);
+int gsb_lbfgs_advance(void* state, float* theta, const float* result, float* summary, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
