@@ -55,6 +55,9 @@ def parse():
     ap.add_argument("--track-frames", type=int, default=12)
     ap.add_argument("--slam-frames", type=int, default=300)
     ap.add_argument("--no-sequence", action="store_true")
+    ap.add_argument("--monocular", action="store_true",
+                    help="also run the sequence leg without depth input (gauge-free: its error against the ground "
+                         "truth is not meaningful on the synthetic scene)")
     ap.add_argument("--det", action="store_true", help="run every leg in deterministic accumulation mode")
     ap.add_argument("--no-f64", action="store_true", help="skip the float64 oracle run of the parity report")
     ap.add_argument("--no-cfg1", action="store_true", help="skip the 10k-Gaussian 320x240 leg (BASELINE configs[0])")
@@ -853,7 +856,7 @@ def run_ours(args):
         except Exception as e:   # noqa: BLE001
             track_frames = {"error": f"{type(e).__name__}: {e}", "where": traceback.format_exc().splitlines()[-12:]}
         slam_seq = {}
-        for mode, rgbd in (("rgbd", True), ("monocular", False)):
+        for mode, rgbd in (("rgbd", True), ("monocular", False)) if args.monocular else (("rgbd", True),):
             try:
                 slam_seq[mode] = slam_sequence_leg(args, dev, rgbd)
             except Exception as e:   # noqa: BLE001

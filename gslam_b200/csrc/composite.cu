@@ -26,8 +26,11 @@
 GSB_TRACE_DEFINE(g_trace_fwd, gsb_debug_trace_fwd)
 #endif
 
+#ifndef FWD_MINB
+#define FWD_MINB 1          // A/B knob, as in composite_bwd.cu
+#endif
 template <bool COUNT, bool STATS>
-__global__ void __launch_bounds__(CMP_THREADS)
+__global__ void __launch_bounds__(CMP_THREADS, FWD_MINB)
 composite_fwd_kernel(const float4* __restrict__ rec, const int32_t* __restrict__ flatten_ids,
                      const int32_t* __restrict__ offsets, const float* __restrict__ backgrounds,
                      int n_lin, int width, int height, int tile_w, int tile_h, int64_t n_isects,

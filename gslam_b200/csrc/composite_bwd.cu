@@ -46,8 +46,11 @@ __device__ __forceinline__ void sts32(unsigned addr, float v) {
 // DET: instead of three float4 atomics, a finished row goes to det_rows[(q * det_cap + li) * 3] (q: the
 // unit inside its tile, li: the entry's list index) and its bit is set in det_mask; the gather kernel
 // below then sums the rows of every Gaussian in a fixed order (bit-reproducible gradients).
+#ifndef BWD_MINB
+#define BWD_MINB 1          // A/B knob (make variant EXTRA=-DBWD_MINB=..): resident CTAs per SM the registers must allow
+#endif
 template <bool DET>
-__global__ void __launch_bounds__(CMP_THREADS)
+__global__ void __launch_bounds__(CMP_THREADS, BWD_MINB)
 composite_bwd_kernel(const float4* __restrict__ rec, const int32_t* __restrict__ flatten_ids,
                      const int32_t* __restrict__ offsets, const float* __restrict__ backgrounds,
                      int n_lin, int width, int height, int tile_w, int tile_h, int64_t n_isects,
@@ -197,7 +200,9 @@ composite_bwd_kernel(const float4* __restrict__ rec, const int32_t* __restrict__
             // Phase 2: per 8x4 block, a warp-uniform branch; inside, misses are predicated (alpha = 0)
 #pragma unroll
             for (int j = 0; j < PPT; ++j) {
+#ifndef BWD_NOSKIP
                 if (votes[j] == 0u) continue;
+#endif
                 const float al = valid[j] ? alpha[j] : 0.f;
                 const float ra = fast_rcp(1.0f - al);
                 const float Tn = T[j] * ra;          // transmittance in front of this splat

@@ -143,7 +143,13 @@ __device__ __forceinline__ void build_sigma(const float* q, const float* ls, flo
     mat3_mul_bt(M, M, Sig);
 }
 
-__global__ void __launch_bounds__(256)
+#ifndef PF_THREADS
+#define PF_THREADS 256      // A/B knobs (make variant): block size and resident blocks the registers must allow
+#endif
+#ifndef PF_MINB
+#define PF_MINB 1
+#endif
+__global__ void __launch_bounds__(PF_THREADS, PF_MINB)
 project_fwd_kernel(const float* __restrict__ means, const float* __restrict__ quats,
                    const float* __restrict__ log_scales, const float* __restrict__ logit_opac,
                    const float* __restrict__ logit_colors, const float* __restrict__ log_unc,
@@ -231,8 +237,8 @@ GSB_API int gsb_project_fwd(const float* means, const float* quats, const float*
     GSB_CHECK_ARG(logit_colors || sh_coeffs);
     GSB_CHECK_ARG(!sh_coeffs || (sh_degree >= 0 && sh_degree <= 3 && sh_stride >= (sh_degree + 1) * (sh_degree + 1)));
     GSB_CHECK_ARG(radii && means2d && rec && tiles_per_gauss);
-    int blocks = (N + 255) / 256;
-    project_fwd_kernel<<<blocks, 256, 0, gsb_stream(stream)>>>(
+    int blocks = (N + PF_THREADS - 1) / PF_THREADS;
+    project_fwd_kernel<<<blocks, PF_THREADS, 0, gsb_stream(stream)>>>(
         means, quats, log_scales, logit_opacities, logit_colors, log_unc, viewmats, Ks, C, N, width,
         height, eps2d, near_plane, far_plane, radius_clip, tile_w, tile_h, radii, means2d, rec,
         tiles_per_gauss, tile_counts, sh_coeffs, sh_degree, sh_stride);

@@ -95,3 +95,84 @@ def test_backproject_matches_the_pinhole_model():
     assert torch.allclose(pts[..., 2], depth)
     assert abs(float(pts[10, 20, 0]) - (20 - float(K[0, 2])) * 3.0 / float(K[0, 0])) < 1e-5
     assert abs(float(pts[10, 20, 1]) - (10 - float(K[1, 2])) * 3.0 / float(K[1, 1])) < 1e-5
+
+
+def _reference_proposal(depthmap, alphas, K, pose, img, splat_scales, N, min_alpha, depth_var, no_depth_var,
+                        initial_opacity, insert_in_regions_with_depth, gt_depthmap=None):
+    """A literal restatement of the proposal half of InsertFromDepthMap.step, reference
+    gslam/insertion.py:128-243 (statement order, in-place updates and RNG draws as there: randn_like, randint
+    over the open pixels, randint over the covered pixels, rand for the quaternions), with the Camera /
+    Frame accessors inlined (gslam/primitives.py:369-395).  Test oracle for gslam_b200.insertion.propose."""
+    depths = (depthmap if gt_depthmap is None else gt_depthmap).clone()
+    valid = torch.logical_and(alphas > min_alpha, depths > 0)
+    n_valid = valid.sum().item()
+    n_invalid = depths.shape.numel() - n_valid
+    n_invalid_splats = min(N, n_invalid)
+    n_valid_splats = max(0, min(int(N / 2) - n_invalid_splats, n_valid))
+    if n_invalid_splats <= 0 and (not insert_in_regions_with_depth and n_valid_splats <= 0):
+        return None
+    median_depth = depths[valid].median() if valid.any() else depths.median()
+    random_depths = torch.randn_like(depths)
+    depths[valid] += random_depths[valid] * depth_var
+    depths[~valid] = median_depth
+    depths[~valid] += random_depths[~valid] * no_depth_var
+    depths.clamp_min_(0.1)
+    idx_valid = torch.nonzero(valid.reshape(-1))
+    idx_invalid = torch.nonzero(~valid.reshape(-1))
+    picks = []
+    if n_invalid_splats > 0:
+        picks.append(idx_invalid[torch.randint(idx_invalid.shape[0], [n_invalid_splats])].reshape(-1))
+    if insert_in_regions_with_depth and n_valid_splats > 0:
+        picks.append(idx_valid[torch.randint(idx_valid.shape[0], [n_valid_splats])].reshape(-1))
+    if len(picks) == 0:
+        return None
+    picks = torch.cat(picks)
+    n = picks.shape[0]
+    H, W = depths.shape
+    v, u = torch.meshgrid(torch.arange(H, dtype=depths.dtype), torch.arange(W, dtype=depths.dtype), indexing="ij")
+    pts = torch.stack([(u - K[0, 2]) * depths / K[0, 0], (v - K[1, 2]) * depths / K[1, 1], depths], -1).reshape(-1, 3)
+    means = pts[picks]
+    colors = img.reshape([-1, 3])[picks]
+    c2w = torch.linalg.inv(pose)
+    means = means @ c2w[:3, :3].t() + c2w[:3, 3]
+    scales = torch.exp(splat_scales).median(dim=0)[0].tile([n, 1])
+    return {"means": means, "scales": torch.log(scales), "colors": torch.logit(colors),
+            "opacities": torch.logit(torch.full((n,), initial_opacity)), "quats": torch.rand((n, 4)),
+            "log_uncertainties": torch.ones((n,))}
+
+
+def test_proposal_matches_a_literal_restatement_of_the_reference_draw_for_draw():
+    """Same seed, same draws, same candidates: the proposal of gslam_b200.insertion against the
+    reference's statement sequence, for a mixed covered / open frame, an all-open frame, and RGB-D input."""
+    K, W, H = intrinsics("tum", 0.1)
+    g = torch.Generator().manual_seed(5)
+    pose = torch.eye(4)
+    pose[:3, 3] = torch.tensor([0.05, -0.02, 0.1])
+    ang = 0.1
+    pose[:3, :3] = torch.tensor([[math.cos(ang), 0, math.sin(ang)], [0, 1, 0], [-math.sin(ang), 0, math.cos(ang)]])
+    img = torch.rand(H, W, 3, generator=g) * 0.98 + 0.01
+    splat_scales = torch.log(0.01 + 0.02 * torch.rand(500, 3, generator=g))
+    depthmap = 1.0 + torch.rand(H, W, generator=g)
+    gt_depth = 2.0 + torch.rand(H, W, generator=g)
+    gt_depth[:3] = 0.0
+    cases = []
+    a_mixed = torch.rand(H, W, generator=g)                    # ~90 % covered at min_alpha 0.1
+    cases.append(("mixed", a_mixed, 40, True, None))
+    cases.append(("mostly covered, covered region allowed", (a_mixed > 0.002).float(), 300, True, None))
+    cases.append(("covered region not allowed", a_mixed, 40, False, None))
+    cases.append(("all open", torch.zeros(H, W), 25, True, None))
+    cases.append(("rgbd", a_mixed, 60, True, gt_depth))
+    for name, alphas, N, allow, gtd in cases:
+        ins = InsertFromDepthMap(0.1, 0.2, 0.1, 0.3, allow)
+        out = RasterizationOutput(None, alphas[None, ..., None].clone(), depthmap[None].clone())
+        torch.manual_seed(1234)
+        ref = _reference_proposal(depthmap, alphas, K, pose, img, splat_scales, N, 0.1, 0.1, 0.2, 0.3, allow, gtd)
+        torch.manual_seed(1234)
+        ours = ins.propose(out, K, pose, img, torch.exp(splat_scales).median(dim=0)[0], N, gtd, generator=None)
+        assert (ref is None) == (ours is None), name
+        if ref is None:
+            continue
+        assert set(ref) == set(ours), name
+        for k in ref:
+            assert ref[k].shape == ours[k].shape, (name, k)
+            torch.testing.assert_close(ours[k], ref[k], rtol=1e-5, atol=1e-6, msg=f"{name}: {k}")
