@@ -64,12 +64,17 @@ def parse():
     return ap.parse_args()
 
 
+# the sources that define the kernels of the tracking step (what profiles/traffic.json quotes DRAM bytes for)
+TRAFFIC_SOURCES = ("common.cuh", "composite.cuh", "composite.cu", "composite_bwd.cu", "project.cu", "binning.cu",
+                   "loss.cu", "sh.cuh", "trace.cuh")
+
+
 def csrc_sha() -> str:
-    """Hash of the kernel sources (gslam_b200/csrc/*, include/gsb.h): what a profile belongs to."""
+    """Hash of the sources of the measured kernels: what a committed profile belongs to."""
     import hashlib
     h = hashlib.sha256()
     d = os.path.join(ROOT, "gslam_b200", "csrc")
-    for fn in sorted(os.listdir(d)) + ["../../include/gsb.h"]:
+    for fn in TRAFFIC_SOURCES:
         with open(os.path.join(d, fn), "rb") as f:
             h.update(fn.encode() + b"\0" + f.read())
     return h.hexdigest()[:12]

@@ -35,7 +35,7 @@ for r in rows[2:]:
     b = float(r[rd]) * UNIT[units[rd]] + float(r[wr]) * UNIT[units[wr]]
     acc.setdefault(key, []).append((b, float(r[du])))
 res = {"source": rep.split("/")[-1], "csrc_sha": csrc_sha(),
-       "captured": datetime.datetime.utcnow().strftime("%Y-%m-%dT%H:%MZ"), "note": "mean over the captured launches; ncu serialises kernels and flushes caches, so "
+       "captured": datetime.datetime.now(datetime.timezone.utc).strftime("%Y-%m-%dT%H:%MZ"), "note": "mean over the captured launches; ncu serialises kernels and flushes caches, so "
        "inputs that the previous kernel left in L2 during a real step are re-read from DRAM here",
        "dram_bytes_per_launch": {k: round(sum(x[0] for x in v) / len(v)) for k, v in acc.items()},
        "ncu_us_per_launch": {k: round(sum(x[1] for x in v) / len(v), 2) for k, v in acc.items()},
