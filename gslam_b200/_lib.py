@@ -53,6 +53,8 @@ SIGNATURES = {
     "gsb_composite_bwd": (_i, [_p] * 4 + [_i] * 6 + [_l] + [_p] * 6 + [_p, _p, _p, _z] + [_p]),
     "gsb_composite_bwd_det_bytes": (_z, [_l]),
     "gsb_map_update": (_i, [_p, _i, _p, _l, _i, _l, _l, _i, _f, _i, _f, _f, _f, _f, _i, _p, _p, _p, _p, _p]),
+    "gsb_isotropic_reg_static_max_n": (_l, []),
+    "gsb_isotropic_reg_static": (_i, [_p, _p, _l, _f, _p, _p, _p]),
     "gsb_map_update_mc_scratch_floats": (_z, [_l, _l]),
     "gsb_map_update_mc": (_i, [_p, _p, _i, _p, _l, _i, _l, _l, _i, _f, _i, _f, _f, _f, _f, _i, _p, _p, _p, _p, _i, _p, _p]),
     "gsb_vis_count": (_i, [_p, _i, _l, _p, _p]),

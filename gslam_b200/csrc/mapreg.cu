@@ -70,3 +70,55 @@ GSB_API int gsb_isotropic_reg(const float* log_scales, const int32_t* vis_count,
     if (loss_sum && det_partials) return gsb_det_sum_launch(det_partials, blocks, loss_sum, gsb_stream(stream));
     return 0;
 }
+
+// ---------------------------------------------------------------------------
+// Allocation-free variant of gsb_isotropic_reg's deterministic mode (no counterpart in the reference;
+// added for callers that cannot allocate device memory: code
+// under CUDA-graph capture, tight serving loops, harnesses that forbid cudaMalloc).  The per-block
+// partial sums live in a file-scope device array instead of caller scratch: 64 Ki floats = 256 KiB,
+// held by every GPU that loads the library until the process exits -> N <= 256 * 65536 = 16 777 216.
+// In host code the array's NAME is a host-side stand-in, not a device address; the address is taken
+// once per device with cudaGetSymbolAddress (with that device current) and cached.
+// Every call on a device shares the array and finds the previous call's partials in it: the kernel
+// overwrites partials[0 .. ceil(N/256)) (every block stores its sum, zero included) and the fixed-order
+// sum reads exactly that range, so nothing has to be cleared -- but two calls that OVERLAP on one GPU
+// (different streams, no ordering between them) race on it.  Calls on one stream are safe.
+// ---------------------------------------------------------------------------
+#define GSB_ISO_STATIC_MAX_BLOCKS 65536
+static __device__ __align__(256) float g_iso_static_scratch[GSB_ISO_STATIC_MAX_BLOCKS];
+#define GSB_MAX_DEVICES 64
+static float* g_iso_static_ptr[GSB_MAX_DEVICES];        // device address of the array, per device (0: not taken yet)
+
+GSB_API int64_t gsb_isotropic_reg_static_max_n(void) { return (int64_t)GSB_ISO_STATIC_MAX_BLOCKS * 256; }
+
+GSB_API int gsb_isotropic_reg_static(const float* log_scales, const int32_t* vis_count, int64_t N, float weight,
+                                     float* v_log_scales, float* loss_sum, void* stream) {
+    GSB_CHECK_ARG(N >= 0);
+    if (N > gsb_isotropic_reg_static_max_n()) {
+        gsb_set_error("gsb_isotropic_reg_static: N = %lld exceeds the static scratch (at most %lld Gaussians); "
+                      "use gsb_isotropic_reg with caller scratch", (long long)N,
+                      (long long)gsb_isotropic_reg_static_max_n());
+        return GSB_EINVAL;
+    }
+    GSB_CHECK_ARG(loss_sum);
+    if (N == 0) {
+        GSB_CUDA(cudaMemsetAsync(loss_sum, 0, sizeof(float), gsb_stream(stream)));
+        return 0;
+    }
+    GSB_CHECK_ARG(log_scales && vis_count && v_log_scales);
+    int dev = -1;
+    GSB_CUDA(cudaGetDevice(&dev));
+    GSB_CHECK_ARG(dev >= 0 && dev < GSB_MAX_DEVICES);
+    float* scratch = __atomic_load_n(&g_iso_static_ptr[dev], __ATOMIC_ACQUIRE);
+    if (!scratch) {
+        // set-up, once per device, with that device current (racing threads store the same value)
+        GSB_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&scratch), g_iso_static_scratch));
+        GSB_CHECK_ARG(scratch != nullptr);
+        __atomic_store_n(&g_iso_static_ptr[dev], scratch, __ATOMIC_RELEASE);
+    }
+    const unsigned blocks = (unsigned)((N + 255) / 256);
+    isotropic_reg_kernel<<<blocks, 256, 0, gsb_stream(stream)>>>(log_scales, vis_count, N, weight, v_log_scales,
+                                                                loss_sum, scratch);
+    GSB_LAUNCH_CHECK();
+    return gsb_det_sum_launch(scratch, blocks, loss_sum, gsb_stream(stream));
+}

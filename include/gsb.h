@@ -282,6 +282,19 @@ int gsb_map_update(const gsb_map_tensor* tensors_host, int n_tensors, const floa
                    int step, int32_t* step_dev, int32_t* vis_count_out, float* iso_loss_sum,
                    float* det_partials, void* stream);
 
+/* gsb_isotropic_reg in deterministic mode WITHOUT caller scratch and without any allocation.  It has no
+ * counterpart in the reference and was added for callers that cannot
+ * call cudaMalloc (CUDA-graph capture, tight serving loops, harnesses that forbid it).  The per-block partial
+ * sums live in a file-scope `static __device__` array of the library (256 KiB, held by every GPU that loads the
+ * library until exit), so N <= gsb_isotropic_reg_static_max_n() = 16 777 216; larger N returns GSB_EINVAL
+ * with a message.  *loss_sum (required) is OVERWRITTEN with the fixed-order sum, v_log_scales is added to
+ * as in gsb_isotropic_reg; results are bit-identical to gsb_isotropic_reg with det_partials.  All calls on
+ * a device share the array (it keeps the last call's partials; each call overwrites the range it reads, so
+ * nothing needs clearing): calls that overlap on one GPU -- different streams with no ordering -- RACE. */
+int64_t gsb_isotropic_reg_static_max_n(void);
+int gsb_isotropic_reg_static(const float* log_scales, const int32_t* vis_count, int64_t N, float weight,
+                             float* v_log_scales, float* loss_sum, void* stream);
+
 /* The same update as ONE kernel that is also the reduce-scatter before it and the all-gather after it, over
  * NVLink multicast (NVLS; symmetric allocations mapped at a multicast address, e.g. torch symmetric memory):
  * grad_rows_mc is the MULTICAST address of the gradient rows -- every load returns the sum over the GPUs,
