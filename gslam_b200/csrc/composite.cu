@@ -27,8 +27,9 @@ GSB_TRACE_DEFINE(g_trace_fwd, gsb_debug_trace_fwd)
 #endif
 
 #ifndef FWD_MINB
-#define FWD_MINB 1          // A/B knob, as in composite_bwd.cu
-#endif
+#define FWD_MINB 32         // 32 one-warp CTAs per SM = 64 registers: without the bound ptxas takes 76 and only 25 fit
+#endif                      // (measured 75.6 against 78.2 us; the backward kernel is the other way round: 103 registers
+                            // unbounded beat 93 at BWD_MINB=20, 110.7 against 112.6 us)
 template <bool COUNT, bool STATS>
 __global__ void __launch_bounds__(CMP_THREADS, FWD_MINB)
 composite_fwd_kernel(const float4* __restrict__ rec, const int32_t* __restrict__ flatten_ids,
