@@ -156,16 +156,21 @@ def stop_timing() -> dict:
     return {k: (len(v), sum(a.elapsed_time(b) for a, b in v) / len(v)) for k, v in t.items()}
 
 
+_raw_stream = getattr(torch._C, "_cuda_getCurrentRawStream", None)
+_raw_device = getattr(torch._C, "_cuda_getDevice", None)
+
+
 def ptr(t: Optional[torch.Tensor]):
     """Device pointer of a contiguous CUDA tensor (None -> NULL)."""
     if t is None:
         return None
     assert t.is_cuda, "gslam_b200 kernels need CUDA tensors (there is no CPU path)"
+    # kernels are enqueued on the CURRENT device's current stream (stream() below): a tensor of another GPU would
+    # be an illegal address there, or a silent wrong-GPU run with peer access -- fail loudly instead
+    if _raw_device is not None and t.device.index != _raw_device():
+        raise RuntimeError(f"gslam_b200: tensor on cuda:{t.device.index} but the current device is "
+                           f"cuda:{_raw_device()}; wrap the call in torch.cuda.device(tensor.device)")
     return t.data_ptr()
-
-
-_raw_stream = getattr(torch._C, "_cuda_getCurrentRawStream", None)
-_raw_device = getattr(torch._C, "_cuda_getDevice", None)
 
 
 def stream() -> int:

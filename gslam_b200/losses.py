@@ -124,6 +124,12 @@ class _PhotometricSSIM(torch.autograd.Function):
         if ctx.unit_upstream:
             # the caller calls backward() on this loss itself: the incoming gradient is exactly 1
             return v_render, None, v_exp, None, None, None, None, None
+        # the saved gradient buffer is scaled and accumulated into IN PLACE below and returned as is (zero-copy);
+        # a second backward through this node (retain_graph, checkpointing) would scale and accumulate twice
+        if getattr(ctx, "consumed", False):
+            raise RuntimeError("photometric_ssim_loss / tracking_loss: backward() ran twice through the same node; "
+                               "its gradient buffer is single-use (recompute the loss instead of retain_graph=True)")
+        ctx.consumed = True
         call("gsb_scale_by_scalar", ptr(v_render), v_render.numel(), ptr(g), stream())
         if maps is not None:
             img1 = render[..., :3].permute(0, 3, 1, 2)

@@ -109,6 +109,7 @@ class _MappingGraph:
     pos: Tensor
     pose_grads: list             # [(parameter, graph-owned gradient tensor)]
     count: int = 0
+    snap: Optional[list] = None  # copies of everything a replay mutates, taken before each chunk (rollback on overflow)
 
 
 @dataclass
@@ -123,6 +124,7 @@ class SlamStats:
     densified: int = 0
     pose_lbfgs_evals: int = 0
     pose_lbfgs_overflows: int = 0
+    mapping_overflow_rollbacks: int = 0
     t_tracking: float = 0.0
     t_mapping: float = 0.0
     n_splats: int = 0
@@ -322,6 +324,31 @@ class Slam:
         grads = [(q, q.grad) for p in w.poses for q in (p.dR, p.dt)]
         return _MappingGraph(g, box["res"], ring, pos, grads)
 
+    def _replay_state(self, w: "_Window") -> list:
+        """Every tensor a replayed mapping iteration changes: the flat parameter buffer, the Adam moments and
+        device step counter of the splats, the window's poses and their optimizer state."""
+        ts = [self.splats.flat]
+        for st in self.opt.state.values():
+            ts += [st["exp_avg"], st["exp_avg_sq"]]
+        if self.opt._dev_step is not None:
+            ts.append(self.opt._dev_step)
+        for p in w.poses:
+            for q in (p.dR, p.dt):
+                ts.append(q.data)
+                st = self.pose_opt.state.get(q) if self.pose_opt is not None else None
+                if st:
+                    ts += [st["step"], st["exp_avg"], st["exp_avg_sq"]]
+        return ts
+
+    @staticmethod
+    def _copy_all(dst: list, src: list) -> None:
+        on_dev = [(d, s_) for d, s_ in zip(dst, src) if d.is_cuda]
+        if on_dev:
+            torch._foreach_copy_([d for d, _ in on_dev], [s_ for _, s_ in on_dev])
+        for d, s_ in zip(dst, src):
+            if not d.is_cuda:
+                d.copy_(s_)
+
     def optimize_map(self, n_iters: Optional[int] = None, prune: bool = True, regularize: bool = True) -> None:
         """Backend.optimize_map (gslam/backend.py:248-409).
 
@@ -384,6 +411,14 @@ class Slam:
             if graph is None:
                 graph = self._capture_mapping(w)
             start = graph.count
+            # a replay that overflows its captured key buffers renders a truncated image, and the chunk's updates
+            # are applied before the flag is read: keep a copy of everything the chunk mutates and roll back
+            live = self._replay_state(w)
+            if graph.snap is None or len(graph.snap) != len(live):
+                graph.snap = [torch.empty_like(t) for t in live]
+            with torch.no_grad():
+                self._copy_all(graph.snap, live)
+            prev_res = res
             for _ in range(chunk):
                 graph.g.replay()
                 if self.pose_opt is not None:
@@ -397,8 +432,16 @@ class Slam:
             losses = graph.ring.tolist()                        # the chunk's one sync
             if int(graph.g.overflow.item()) != 0:
                 # more intersections than the captured buffers hold: the replayed iterations rendered
-                # a truncated image; from here on iterate eagerly (exact buffers)
+                # a truncated image.  Undo the chunk (parameters, moments, step counters, poses), do not
+                # account its losses, and redo it eagerly (exact buffers) from here on
+                with torch.no_grad():
+                    self._copy_all(live, graph.snap)
+                self.total_step -= chunk
+                done -= chunk
+                res = prev_res
                 use_graph, graph = False, None
+                self.stats.mapping_overflow_rollbacks += 1
+                continue
             for i in range(start, start + chunk):
                 if account(losses[i % len(losses)]):
                     stopped = True

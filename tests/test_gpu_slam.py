@@ -71,3 +71,36 @@ def test_rgbd_sequence_follows_the_ground_truth_trajectory(cuda):
     rel = est[:, :3, :3] @ gt_poses[:, :3, :3].transpose(1, 2)
     assert float((rel - torch.eye(3, device=cuda)).norm(dim=(1, 2)).max()) < 0.2        # < 8 degrees
     assert slam.tracker.gt_depth is not None
+
+
+def test_overflowed_mapping_chunk_is_rolled_back_and_redone_eagerly(cuda, monkeypatch):
+    """A replayed chunk whose renders overflow the captured key buffers must leave no trace: the map, the Adam
+    moments and the step counters after it equal those of a run that never used a graph (deterministic mode, so
+    bit for bit), and the chunk's losses are not accounted."""
+    import gslam_b200.slam as slam_mod
+    from gslam_b200.slam import Slam, synthetic_sequence
+
+    def run(graph_mapping, cripple):
+        cam, imgs, _, _ = synthetic_sequence(2, 6_000, 0.5, cuda)
+        conf = MapConfig(num_iters_initialization=12, deterministic=True, graph_mapping=graph_mapping,
+                         densify_every=0)
+        if cripple:
+            real = slam_mod.GraphedStep
+
+            def tiny(fn, headroom=1.5, n_isects_hint=None, pool=None, **kw):
+                # a key capacity of a tenth of the intersections the step produces: every replay overflows
+                return real(fn, headroom=0.1, n_isects_hint=n_isects_hint, pool=pool, **kw)
+            monkeypatch.setattr(slam_mod, "GraphedStep", tiny)
+        s = Slam(cam, conf, TrackingConfig(lbfgs_max_iter=4), cuda)
+        s.process_frame(imgs[0])
+        monkeypatch.undo()
+        return s
+
+    eager = run(False, False)
+    rolled = run(True, True)
+    assert rolled.stats.mapping_overflow_rollbacks >= 1
+    assert rolled.stats.mapping_iters == eager.stats.mapping_iters
+    assert rolled.splats.n == eager.splats.n
+    assert torch.equal(rolled.splats.flat, eager.splats.flat)
+    for a, b in zip(rolled.splats.params, eager.splats.params):
+        assert torch.equal(rolled.opt.state[a]["exp_avg_sq"], eager.opt.state[b]["exp_avg_sq"])
