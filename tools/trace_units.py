@@ -29,7 +29,7 @@ def run():
     out.render.sum().backward()
 
 
-for _ in range(3):
+for _ in range(5):
     run()
 torch.cuda.synchronize()
 L = ctypes.CDLL(_lib.LIB_PATH)
@@ -38,6 +38,7 @@ buf = np.zeros(4 * 65536, dtype=np.uint64)      # GSB_TRACE_UNITS items of 4 wor
 rc = getattr(L, "gsb_debug_trace_" + which)(buf.ctypes.data_as(ctypes.c_void_p), buf.size // 4)
 t = buf.reshape(-1, 4)
 t = t[t[:, 1] > 0]
+t = t[t[:, 0] + np.uint64(1_000_000) > t[:, 0].max()]      # the last run only (split ids of earlier runs linger)
 t0 = t[:, 0].min()
 beg, end = (t[:, 0] - t0).astype(np.int64), (t[:, 1] - t0).astype(np.int64)
 dur, sm = end - beg, t[:, 2].astype(np.int64)
@@ -55,3 +56,16 @@ print("per-SM kept entries: min %d mean %.0f max %d;  units per SM: min %d max %
 print("corr(SM work, SM finish) = %.3f;  sum(unit time) / kept entries = %.1f ns" % (np.corrcoef(work, ends)[0, 1], dur.sum() / max(kept.sum(), 1)))
 ts = np.linspace(0, end.max(), 21)
 print("alive units at 0,5,..100 %% of the span:", [int(((beg <= x) & (end > x)).sum()) for x in ts])
+mx = np.array([kept[sm == s].max() for s in sms])
+A = np.stack([work, mx, np.ones_like(work)], 1).astype(np.float64)
+coef, res, *_ = np.linalg.lstsq(A, ends.astype(np.float64), rcond=None)
+pred = A @ coef
+print("SM finish ~ %.2f ns x SM kept + %.1f ns x heaviest unit's kept + %.0f ns;  R^2 = %.3f;  corr(finish, heaviest) = %.3f"
+      % (coef[0], coef[1], coef[2], 1 - ((ends - pred) ** 2).sum() / ((ends - ends.mean()) ** 2).sum(), np.corrcoef(mx, ends)[0, 1]))
+# how a unit's duration depends on its own work and on its SM's load
+smw = {s: w for s, w in zip(sms, work)}
+B = np.stack([kept, np.array([smw[s] for s in sm]), np.ones_like(kept)], 1).astype(np.float64)
+c2, *_ = np.linalg.lstsq(B, dur.astype(np.float64), rcond=None)
+p2 = B @ c2
+print("unit duration ~ %.1f ns x own kept + %.2f ns x SM kept + %.0f ns;  R^2 = %.3f"
+      % (c2[0], c2[1], c2[2], 1 - ((dur - p2) ** 2).sum() / ((dur - dur.mean()) ** 2).sum()))
