@@ -60,6 +60,9 @@ def parse():
                          "truth is not meaningful on the synthetic scene)")
     ap.add_argument("--det", action="store_true", help="run every leg in deterministic accumulation mode")
     ap.add_argument("--no-f64", action="store_true", help="skip the float64 oracle run of the parity report")
+    ap.add_argument("--leg-deadline", type=float, default=420.0,
+                    help="seconds the secondary legs (mapping, sequences, CPU baseline) may take together before "
+                         "rank 0 prints the headline line without them and every rank exits")
     ap.add_argument("--no-cfg1", action="store_true", help="skip the 10k-Gaussian 320x240 leg (BASELINE configs[0])")
     return ap.parse_args()
 
@@ -544,6 +547,7 @@ def slam_sequence_leg(args, dev, rgbd: bool, group="local"):
             "keyframes": st.keyframes, "n_splats": st.n_splats,
             "mapping_iters": st.mapping_iters, "tracking_evals": st.tracking_evals,
             "pose_lbfgs_evals": st.pose_lbfgs_evals, "inserted": st.inserted, "pruned": st.pruned,
+            "overflow_rollbacks": st.mapping_overflow_rollbacks,
             "s_tracking": st.t_tracking, "s_mapping": st.t_mapping,
             "translation_error_m": {"mean": float(err.mean()), "max": float(err.max()),
                                     "path_length": float((gt[1:, :3, 3] - gt[:-1, :3, 3]).norm(dim=1).sum())},
@@ -613,6 +617,15 @@ def cfg1_leg(dev):
             "gpu": {"value": 1e3 / ms, "unit": UNIT, "ms_per_step": ms, "steps": steps,
                     "timed_loop": "CUDA-graph replay, L2 flushed between steps"},
             "parity": parity_report(gpu, ref)}
+
+
+_T0 = time.perf_counter()
+
+
+def progress(msg: str) -> None:
+    """One line per leg on stderr (rank 0): where a run spends its wall time, and where it stopped if it did."""
+    if int(os.environ.get("RANK", "0")) == 0:
+        print(f"[bench {time.perf_counter() - _T0:7.1f} s] {msg}", file=sys.stderr, flush=True)
 
 
 def run_ours(args):
@@ -687,6 +700,7 @@ def run_ours(args):
         step(params, vm, K, gt)
     barrier()
 
+    progress('warm-up done, capturing the step')
     # The step is launch-bound in eager mode (about 50 launches + one host sync), so the timed
     # loop replays a CUDA graph of the SAME step() captured through the public API.
     from gslam_b200.graph import GraphedStep
@@ -764,6 +778,7 @@ def run_ours(args):
     finally:
         ops.isect_capacity = None
 
+    progress('timed loop and per-kernel pass done')
     # ---- e2e: host buffers in, loss + pose gradient out, copies inside the timed region ----------
     h2d = host_arena.numel() * 4        # the pipelined loop copies the whole arena (64-byte padding included)
     res_host = torch.empty(17, dtype=torch.float32).pin_memory()
@@ -874,9 +889,35 @@ def run_ours(args):
     e2e_value = world * 1e3 / float(t[0].item())
     e2e_serial = world * 1e3 / float(t[1].item())
 
+    progress('e2e loops done')
+    # The legs below (mapping, sequences) are secondary: if one of them wedges -- a collective that a rank never
+    # joins -- the headline must still come out.  Every rank arms the same deadline; when it fires rank 0 prints the
+    # line with what is measured so far and every rank leaves.
+    import threading
+
+    def bail():
+        if rank == 0:
+            fallback = {
+                "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": {"workload": workload_string(n, world),
+                           "l2": "256 MiB memset between timed steps, outside each step's event pair"},
+                "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                        "serial_value": e2e_serial},
+                "gpu_launches": launches, "clocks": clocks,
+                "error": f"a secondary leg did not finish within {args.leg_deadline} s (see the [bench] lines on "
+                         "stderr for the last one that did); headline and e2e are complete"}
+            print(json.dumps(fallback), flush=True)
+        sys.stderr.flush()
+        os._exit(0)
+    watchdog = threading.Timer(args.leg_deadline, bail)
+    watchdog.daemon = True
+    watchdog.start()
     mapping = None
     if not args.no_mapping:
         mapping = mapping_leg(args, dev, rank, world)
+    progress('mapping leg done')
     mapping_big = None
     if args.map_big == "on" or (args.map_big == "auto" and world == 8 and not args.no_mapping):
         try:
@@ -884,6 +925,7 @@ def run_ours(args):
         except Exception as e:   # noqa: BLE001  (reported in place; every rank fails or none: the step is collective)
             import traceback as _tb
             mapping_big = {"error": f"{type(e).__name__}: {e}", "where": _tb.format_exc().splitlines()[-8:]}
+    progress('mapping_big leg done' if mapping_big is not None else 'mapping_big leg skipped')
     closure = tracking_closure_leg(args, dev) if rank == 0 else None
     import traceback
     seq_sharded = None
@@ -893,6 +935,7 @@ def run_ours(args):
             seq_sharded = slam_sequence_leg(args, dev, True, group=None)
         except Exception as e:   # noqa: BLE001
             seq_sharded = {"error": f"{type(e).__name__}: {e}", "where": traceback.format_exc().splitlines()[-12:]}
+    progress('sharded sequence leg done' if seq_sharded is not None else 'sharded sequence leg skipped')
     track_frames = slam_seq = None
     if rank == 0 and not args.no_sequence:
         # secondary legs: a failure here is reported in place and must not take the headline line down
@@ -900,6 +943,7 @@ def run_ours(args):
             track_frames = tracking_frames_leg(args, dev)
         except Exception as e:   # noqa: BLE001
             track_frames = {"error": f"{type(e).__name__}: {e}", "where": traceback.format_exc().splitlines()[-12:]}
+        progress('tracking_frames leg done')
         slam_seq = {}
         for mode, rgbd in (("rgbd", True), ("monocular", False)) if args.monocular else (("rgbd", True),):
             try:
@@ -907,6 +951,7 @@ def run_ours(args):
             except Exception as e:   # noqa: BLE001
                 slam_seq[mode] = {"error": f"{type(e).__name__}: {e}", "where": traceback.format_exc().splitlines()[-12:]}
 
+    progress('sequence legs done')
     if rank == 0:
         hbm, which, sm_max = peaks()
         CN, px = n, H * W
@@ -1030,11 +1075,13 @@ def run_ours(args):
         # the mapping object goes LAST so that a truncated tail of the line still carries it
         line["mapping_big"] = line.pop("mapping_big")
         line["mapping"] = line.pop("mapping")
+        watchdog.cancel()
         print(json.dumps(line), flush=True)
         if not parity_ok:
             print("bench.py: PARITY FAILED (see the `parity` object of the line above)", file=sys.stderr, flush=True)
             if world == 1:
                 sys.exit(3)
+    watchdog.cancel()
     if world > 1:
         # Tearing the communicator down while captured graphs that hold NCCL kernels are alive can
         # block in ncclCommDestroy: drop the graphs, agree that everybody is done, and leave.

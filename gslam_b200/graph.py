@@ -86,10 +86,14 @@ class GraphedStep:
             with torch.cuda.stream(side):
                 self.graph.capture_begin(pool=pool) if pool is not None else self.graph.capture_begin()
                 try:
+                    # a step that renders nothing (a rank without a view of a sharded window) must not pick up the
+                    # flag of whatever rasterization() call came last -- a tensor of another graph, or freed memory
+                    ops.last_overflow = None
                     self.loss = fn()
                     # every rasterization() call starts from a cleared flag, so the flag of a replay is
                     # gone with the next one: keep a sticky copy that only reset_overflow() clears
-                    torch.maximum(self.overflow, ops.last_overflow, out=self.overflow)
+                    if ops.last_overflow is not None:
+                        torch.maximum(self.overflow, ops.last_overflow, out=self.overflow)
                 finally:
                     self.graph.capture_end()
             cur.wait_stream(side)

@@ -430,7 +430,13 @@ class Slam:
             done += chunk
             res = graph.res
             losses = graph.ring.tolist()                        # the chunk's one sync
-            if int(graph.g.overflow.item()) != 0:
+            overflowed = graph.g.overflow
+            if self.world > 1:
+                # a rank that redoes a chunk issues the chunk's collectives again: every rank must take the same
+                # branch, so the flag is the MAX over the ranks (one 4-byte all-reduce per chunk)
+                from .mapping import allreduce_max_
+                overflowed = allreduce_max_(overflowed.clone(), self.group)
+            if int(overflowed.item()) != 0:
                 # more intersections than the captured buffers hold: the replayed iterations rendered
                 # a truncated image.  Undo the chunk (parameters, moments, step counters, poses), do not
                 # account its losses, and redo it eagerly (exact buffers) from here on
