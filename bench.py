@@ -551,6 +551,7 @@ def slam_sequence_leg(args, dev, rgbd: bool, group="local"):
             "s_tracking": st.t_tracking, "s_mapping": st.t_mapping,
             "translation_error_m": {"mean": float(err.mean()), "max": float(err.max()),
                                     "path_length": float((gt[1:, :3, 3] - gt[:-1, :3, 3]).norm(dim=1).sum())},
+            "lost_track": bool(float(err.mean()) > 0.25 * float((gt[1:, :3, 3] - gt[:-1, :3, 3]).norm(dim=1).sum())),
             "includes": "frame 0 initialisation (up to 400 mapping iterations)"}
 
 
@@ -907,25 +908,26 @@ def run_ours(args):
                         "serial_value": e2e_serial},
                 "gpu_launches": launches, "clocks": clocks,
                 "error": f"a secondary leg did not finish within {args.leg_deadline} s (see the [bench] lines on "
-                         "stderr for the last one that did); headline and e2e are complete"}
+                         "stderr for the last one that did); headline, e2e and the legs listed here are complete"}
+            full = partial.pop("line", None)
+            if full is not None:                # everything but the last leg (mapping_big) is in: print the whole line
+                fallback = dict(full, error=fallback["error"])
+                fallback["mapping_big"] = {"error": "did not finish before the deadline"}
+            fallback.update(partial)            # the legs that did finish (the mapping object, if there, goes last)
+            if "mapping" in fallback:
+                fallback["mapping"] = fallback.pop("mapping")
             print(json.dumps(fallback), flush=True)
         sys.stderr.flush()
         os._exit(0)
     watchdog = threading.Timer(args.leg_deadline, bail)
     watchdog.daemon = True
     watchdog.start()
+    partial = {}
     mapping = None
     if not args.no_mapping:
         mapping = mapping_leg(args, dev, rank, world)
+    partial["mapping"] = mapping
     progress('mapping leg done')
-    mapping_big = None
-    if args.map_big == "on" or (args.map_big == "auto" and world == 8 and not args.no_mapping):
-        try:
-            mapping_big = mapping_big_leg(args, dev, rank, world)
-        except Exception as e:   # noqa: BLE001  (reported in place; every rank fails or none: the step is collective)
-            import traceback as _tb
-            mapping_big = {"error": f"{type(e).__name__}: {e}", "where": _tb.format_exc().splitlines()[-8:]}
-    progress('mapping_big leg done' if mapping_big is not None else 'mapping_big leg skipped')
     closure = tracking_closure_leg(args, dev) if rank == 0 else None
     import traceback
     seq_sharded = None
@@ -935,6 +937,7 @@ def run_ours(args):
             seq_sharded = slam_sequence_leg(args, dev, True, group=None)
         except Exception as e:   # noqa: BLE001
             seq_sharded = {"error": f"{type(e).__name__}: {e}", "where": traceback.format_exc().splitlines()[-12:]}
+    partial["sequence_sharded"] = seq_sharded
     progress('sharded sequence leg done' if seq_sharded is not None else 'sharded sequence leg skipped')
     track_frames = slam_seq = None
     if rank == 0 and not args.no_sequence:
@@ -951,7 +954,9 @@ def run_ours(args):
             except Exception as e:   # noqa: BLE001
                 slam_seq[mode] = {"error": f"{type(e).__name__}: {e}", "where": traceback.format_exc().splitlines()[-12:]}
 
+    partial.update({"tracking_closure": closure, "tracking_frames": track_frames, "sequence": slam_seq})
     progress('sequence legs done')
+    mapping_big = None
     if rank == 0:
         hbm, which, sm_max = peaks()
         CN, px = n, H * W
@@ -1072,8 +1077,19 @@ def run_ours(args):
                     line["cfg1"] = {"error": f"{type(e).__name__}: {e}",
                                     "where": traceback.format_exc().splitlines()[-12:]}
                     parity_ok = False
+        partial["line"] = line
+    # the 3 M-Gaussian leg last: the one that moves the most memory through the fabric cannot take the others with it
+    if args.map_big == "on" or (args.map_big == "auto" and world == 8 and not args.no_mapping):
+        try:
+            mapping_big = mapping_big_leg(args, dev, rank, world)
+        except Exception as e:   # noqa: BLE001  (reported in place; every rank fails or none: the step is collective)
+            import traceback as _tb
+            mapping_big = {"error": f"{type(e).__name__}: {e}", "where": _tb.format_exc().splitlines()[-8:]}
+    progress('mapping_big leg done' if mapping_big is not None else 'mapping_big leg skipped')
+    if rank == 0:
         # the mapping object goes LAST so that a truncated tail of the line still carries it
-        line["mapping_big"] = line.pop("mapping_big")
+        line.pop("mapping_big", None)
+        line["mapping_big"] = mapping_big
         line["mapping"] = line.pop("mapping")
         watchdog.cancel()
         print(json.dumps(line), flush=True)
