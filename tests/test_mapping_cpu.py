@@ -29,7 +29,8 @@ def _make_step(splats, **kw):
                        collect_grads=S.collect_grads, depth_tv_weight=1e-6, **kw)
 
 
-def _run(rank, world, port, q):
+def _run(rank, world, port, q, n_views=None):
+    N_VIEWS = n_views or globals()["N_VIEWS"]
     if world > 1:
         os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
         dist.init_process_group("gloo", rank=rank, world_size=world)
@@ -106,6 +107,26 @@ def test_two_ranks_match_one_rank_over_three_steps():
         assert (v == v1).all()
     # the ranks stay bit-identical: every row is updated by exactly one rank and all-gathered
     assert (two[0][1] == two[1][1]).all() and two[0][2] == two[1][2]
+
+
+def _run_three_views(rank, world, port, q):
+    _run(rank, world, port, q, n_views=3)
+
+
+@pytest.mark.timeout(1500)
+def test_eight_ranks_with_five_viewless_ranks_match_one_rank():
+    """More ranks than views (the first keyframes of a sequence on 8 GPUs): the ranks without a view contribute
+    zero rows, still join every collective, update their own Gaussian range and end with the same parameters."""
+    one = _launch(1, _run_three_views)[0]
+    eight = _launch(8, _run_three_views)
+    p1 = torch.from_numpy(one[1])
+    for _, p, l, v, cap in eight:
+        assert cap == 608                       # 601 rounded up to the 8 ranks
+        torch.testing.assert_close(torch.from_numpy(p), p1, rtol=2e-4, atol=2e-6)
+        for a, b in zip(l, one[2]):
+            assert abs(a - b) < 1e-5 * max(1.0, abs(b))
+        assert (v == one[3]).all()
+        assert (p == eight[0][1]).all() and l == eight[0][2]
 
 
 def test_stub_update_matches_torch_adam_and_autograd_regulariser():
