@@ -181,6 +181,43 @@ def allreduce_max_(t: Tensor, group=None) -> Tensor:
     return t
 
 
+@torch.no_grad()
+def gather_adam_state(splats: "FlatSplats", optimizer, group=None) -> None:
+    """Make every rank's Adam moments complete.  A view-sharded step updates the moments of Gaussian g only on the
+    rank whose range [r * cap / p, (r + 1) * cap / p) holds g; everywhere else they are stale.  That is fine while
+    the ranges stand still, but anything that changes N or the capacity (insertion, densification, pruning: the
+    compaction moves every later Gaussian down, the new capacity moves every boundary) hands Gaussians to ranks
+    that never updated their moments -- on 8 ranks with a few thousand splats most of the map after a few
+    keyframes.  So before the Gaussians are re-partitioned every rank collects all moments by the CURRENT ranges:
+    one all-gather of [cap / p, 2 * sum(widths)] floats.  After it any partition is valid."""
+    rank, world = _world(group)
+    if world == 1 or optimizer is None or splats.n == 0:
+        return
+    n, per = splats.n, splats.cap // world
+    tensors = []
+    for prm, w in zip(splats.params, splats.widths):
+        st = optimizer.state.get(prm)
+        if st and "exp_avg" in st:
+            tensors += [(st["exp_avg"], w), (st["exp_avg_sq"], w)]
+    if not tensors:
+        return
+    dev = splats.flat.device
+    width = sum(w for _, w in tensors)
+    send = torch.zeros(per, width, dtype=torch.float32, device=dev)
+    lo, hi = min(rank * per, n), min((rank + 1) * per, n)
+    col = 0
+    for t, w in tensors:
+        if hi > lo:
+            send[:hi - lo, col:col + w] = t.reshape(n, w)[lo:hi]
+        col += w
+    recv = torch.empty(world * per, width, dtype=torch.float32, device=dev)
+    dist.all_gather_into_tensor(recv.view(-1), send.view(-1), group=group)
+    col = 0
+    for t, w in tensors:
+        t.reshape(n, w).copy_(recv[:n, col:col + w])
+        col += w
+
+
 def _coalesced(group, device):
     """One NCCL group call for several collectives (a capability of the backend, not a fallback: gloo has
     no coalescing and simply issues them one by one)."""

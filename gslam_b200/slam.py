@@ -39,7 +39,8 @@ from .losses import photometric_ssim_loss
 from .graph import GraphedStep, shared_pool
 from .insertion import InsertFromDepthMap, InsertUsingImagePlaneGradients, KeyframeView
 from .map import GaussianSplattingData
-from .mapping import DEFAULT_LRS, LOCAL, PARAM_NAMES, FlatSplats, MappingStep, _world, allreduce_sum_
+from .mapping import (DEFAULT_LRS, LOCAL, PARAM_NAMES, FlatSplats, MappingStep, _world, allreduce_sum_,
+                      gather_adam_state)
 from .optim import FusedAdam
 from .primitives import Camera, PoseZhou, pose_batch
 from .pruning import prune_round
@@ -188,6 +189,12 @@ class Slam:
                              self.camera.height, packed=False, render_mode="RGB+D", log_uncertainties=P[5],
                              backgrounds=self.bg1.expand(C, 3).contiguous())
 
+    def _before_surgery(self) -> None:
+        """A view-sharded step keeps a Gaussian's Adam moments current only on the rank that owns its range; insertion,
+        densification and pruning re-partition the Gaussians, so every rank first collects all moments."""
+        if self.world > 1:
+            gather_adam_state(self.splats, self.opt, self.group)
+
     def _pose_batch(self, poses) -> Tensor:
         return pose_batch(poses) if poses else torch.zeros(0, 4, 4, device=self.dev)
 
@@ -209,6 +216,7 @@ class Slam:
         pose = PoseZhou(torch.eye(4, device=d)).to(d)
         kf = Keyframe(0, img, pose, torch.zeros(2, device=d), gt_depth=gt_depth)
         self.keyframes[0] = kf
+        self._before_surgery()
         self.stats.inserted += self.insertion.step(self.splats, self.opt, mock, self.camera.intrinsics,
                                                    torch.eye(4, device=d), img, self.conf.n_init_splats,
                                                    gt_depthmap=gt_depth if self.conf.use_gt_depths else None,
@@ -220,6 +228,7 @@ class Slam:
         """Backend.add_keyframe (gslam/backend.py:633-679)."""
         out = self.render(viewmat.view(1, 4, 4))
         out.depthmaps = out.depthmaps * self.conf.initial_scale
+        self._before_surgery()
         self.stats.inserted += self.insertion.step(self.splats, self.opt, out, self.camera.intrinsics, viewmat,
                                                    img, self.conf.n_keyframe_splats, keyframes=self._views(),
                                                    generator=self.gen)
@@ -267,6 +276,7 @@ class Slam:
             # the reference densifies between backward and the optimizer step (:328-351): the
             # parameters it re-creates carry no gradient, so that iteration takes no splat step and
             # only the opacity decay applies (radii padded with zeros for the new rows)
+            self._before_surgery()
             n_dup, n_split = self.insertion_3dgs.step(self.splats, self.opt, res.outputs, self.gen,
                                                       group=self.group, n_views_total=self._n_window)
             self.stats.inserted += n_dup + n_split
@@ -465,6 +475,7 @@ class Slam:
             if self.world > 1:
                 self._share_window(window_all, pos)
             if prune:
+                self._before_surgery()
                 self.stats.pruned += prune_round(
                     self.splats, self.opt, res.radii, res.n_touched, c.opacity_pruning_threshold,
                     c.size_pruning_threshold, 3 if c.enable_visibility_pruning else None,
@@ -500,6 +511,7 @@ class Slam:
         last = self.keyframes[max(self.keyframes)]
         out = self.render(last.pose().view(1, 4, 4))
         c = self.conf
+        self._before_surgery()
         self.stats.pruned += prune_round(self.splats, self.opt, out.radii, out.n_touched,
                                          c.opacity_pruning_threshold, c.size_pruning_threshold, None,
                                          c.optim_window_last_n_keyframes, group=LOCAL)   # replicated: no collective

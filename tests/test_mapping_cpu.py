@@ -129,6 +129,43 @@ def test_eight_ranks_with_five_viewless_ranks_match_one_rank():
         assert (p == eight[0][1]).all() and l == eight[0][2]
 
 
+def _run_gather_moments(rank, world, port, q):
+    """Every rank holds the true Adam moments only inside its own Gaussian range (garbage elsewhere: what a sharded
+    step leaves behind); after gather_adam_state every rank must hold all of them."""
+    from types import SimpleNamespace
+    from gslam_b200.mapping import gather_adam_state
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    sc = make_scene(N_GAUSS, 1, "tum", 0.1)
+    tensors = list(sc.params())
+    tensors[4] = torch.randn(N_GAUSS, 4, 3)                    # SH coefficients: a 12-float block
+    splats = FlatSplats(tensors, align=world)
+    g = torch.Generator().manual_seed(11)
+    truth = {k: (torch.randn(p.shape, generator=g), torch.rand(p.shape, generator=g)) for k, p in enumerate(splats.params)}
+    per = splats.cap // world
+    lo, hi = min(rank * per, N_GAUSS), min((rank + 1) * per, N_GAUSS)
+    state = {}
+    for k, p in enumerate(splats.params):
+        m, v = torch.full(p.shape, float("nan")), torch.full(p.shape, float("nan"))
+        m[lo:hi], v[lo:hi] = truth[k][0][lo:hi], truth[k][1][lo:hi]
+        state[p] = {"exp_avg": m, "exp_avg_sq": v}
+    opt = SimpleNamespace(state=state)
+    gather_adam_state(splats, opt, None)
+    ok = all(torch.equal(state[p]["exp_avg"], truth[k][0]) and torch.equal(state[p]["exp_avg_sq"], truth[k][1])
+             for k, p in enumerate(splats.params))
+    q.put((rank, ok, hi - lo))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.timeout(600)
+@pytest.mark.parametrize("world", [3, 8])
+def test_adam_moments_are_complete_on_every_rank_before_a_repartition(world):
+    out = _launch(world, _run_gather_moments)
+    assert all(ok for _, ok, _ in out)
+    assert sum(n for _, _, n in out) == N_GAUSS
+
+
 def test_stub_update_matches_torch_adam_and_autograd_regulariser():
     """The torch restatement the CPU tests inject (and the GPU test compares gsb_map_update with) against
     torch.optim.Adam + autograd of the reference's isotropic loss + the masked opacity decay."""
