@@ -15,7 +15,8 @@ torch.cuda.set_device(local)
 dev = torch.device("cuda", local)
 dist.init_process_group("nccl", device_id=dev)
 F = int(sys.argv[1]) if len(sys.argv) > 1 else 60
-for graph in (True, False):
+modes = (True,) if len(sys.argv) > 2 and sys.argv[2] == "graph-only" else (True, False)
+for graph in modes:
     slam, fps, gt = run_sequence(F, n_gauss=20_000, scale=1.0, device=dev,
                                  map_conf=MapConfig(use_gt_depths=True, deterministic=True, graph_mapping=graph),
                                  group=None)
@@ -30,7 +31,7 @@ for graph in (True, False):
         same = all(torch.equal(s, sigs[0]) for s in sigs)
         print(f"graph={graph} world={dist.get_world_size()} frames={F} fps={fps:.1f} keyframes={st.keyframes} n_splats={st.n_splats} "
               f"iters={st.mapping_iters} rollbacks={st.mapping_overflow_rollbacks} inserted={st.inserted} pruned={st.pruned} "
-              f"err_mean={float(err.mean()):.4f} err@10,20,30,40,59={[round(float(err[i]), 4) for i in (10, 20, 30, 40, min(59, F - 1))]} "
+              f"err_mean={float(err.mean()):.4f} err@10,20,30,40,59={[round(float(err[min(i, F - 1)]), 4) for i in (10, 20, 30, 40, 59)]} "
               f"same_map_on_all_ranks={same} |param|max={float(sigs[0][1]):.3g}", flush=True)
     del slam
     torch.cuda.empty_cache()
