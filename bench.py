@@ -919,10 +919,10 @@ def run_ours(args):
             print(json.dumps(fallback), flush=True)
         sys.stderr.flush()
         os._exit(0)
+    partial = {}
     watchdog = threading.Timer(args.leg_deadline, bail)
     watchdog.daemon = True
     watchdog.start()
-    partial = {}
     mapping = None
     if not args.no_mapping:
         mapping = mapping_leg(args, dev, rank, world)
